@@ -1,0 +1,22 @@
+"""htool_python_b200 -- B200-native engine for the H-matrix product path of htool-ddm/htool_python.
+
+Scope: `HMatrix.__mul__/__matmul__` and the operators behind `DistributedOperator`'s matvec/matmat.
+The H-matrix is assembled by the reference; `FlatHMatrix.from_htool` flattens it, `Engine`/`B200HMatrix` serve the
+products from hand-written sm_100a kernels (libhmb200.so, C ABI in include/hmb200.h).
+"""
+from .flat import FlatHMatrix  # noqa: F401
+
+__all__ = ["FlatHMatrix", "Engine", "B200HMatrix", "bridge"]
+
+
+def __getattr__(name):
+    if name == "Engine":
+        from .engine import Engine
+        return Engine
+    if name == "B200HMatrix":
+        from .hmatrix import B200HMatrix
+        return B200HMatrix
+    if name == "bridge":
+        import importlib
+        return importlib.import_module(".bridge", __name__)
+    raise AttributeError(name)

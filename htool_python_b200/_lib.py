@@ -1,0 +1,72 @@
+"""ctypes binding of libhmb200.so (include/hmb200.h).  There is no fallback: a missing library is an error."""
+from __future__ import annotations
+
+import ctypes
+from ctypes import POINTER, c_char, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_void_p
+from pathlib import Path
+
+from .flat import hmb200_flat
+
+HOST, DEVICE = 0, 1
+LIB_PATH = Path(__file__).resolve().parent / "libhmb200.so"
+
+
+class hmb200_options(ctypes.Structure):
+    _fields_ = [(n, c_int32) for n in ("stage_bytes", "stage_z_bytes", "n_stages", "consumer_warps", "piece1_bytes", "piece2_bytes",
+                                       "bin_rows", "unit_stages", "ctas", "build_transpose")] + [("reserved", c_int32 * 6)]
+
+
+class hmb200_info(ctypes.Structure):
+    _fields_ = [("n_rows", c_int32), ("n_cols", c_int32), ("is_complex", c_int32), ("n_bins", c_int32),
+                ("n_leaves", c_int64), ("n_pieces1", c_int64), ("n_pieces2", c_int64), ("n_stages1", c_int64),
+                ("n_stages2", c_int64), ("n_reduce_segments", c_int64), ("stream1_bytes", c_int64), ("stream2_bytes", c_int64),
+                ("table_bytes", c_int64), ("workspace_bytes", c_int64), ("stored_coefficients", c_double),
+                ("pack_seconds", c_double), ("upload_seconds", c_double)]
+
+
+EXPORTS = {
+    "hmb200_create_d": (c_void_p, [POINTER(hmb200_flat), c_int, c_void_p, POINTER(hmb200_options)]),
+    "hmb200_create_z": (c_void_p, [POINTER(hmb200_flat), c_int, c_void_p, POINTER(hmb200_options)]),
+    "hmb200_destroy": (None, [c_void_p]),
+    "hmb200_get_info": (c_int, [c_void_p, POINTER(hmb200_info)]),
+    "hmb200_set_stream": (c_int, [c_void_p, c_void_p]),
+    "hmb200_add_vector_product_d": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int]),
+    "hmb200_add_vector_product_z": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int]),
+    "hmb200_add_matrix_product_row_major_d": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int]),
+    "hmb200_add_matrix_product_row_major_z": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int]),
+    "hmb200_permute_gather": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "hmb200_permute_scatter": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "hmb200_set_permutations": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "hmb200_matvec_user_d": (c_int, [c_void_p, c_void_p, c_void_p, c_int]),
+    "hmb200_matvec_user_z": (c_int, [c_void_p, c_void_p, c_void_p, c_int]),
+    "hmb200_matmat_user_d": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int]),
+    "hmb200_matmat_user_z": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int]),
+    "hmb200_last_kernel_ms": (c_int, [c_void_p, POINTER(c_float * 4)]),
+    "hmb200_enable_timing": (c_int, [c_void_p, c_int]),
+    "hmb200_launch_count": (c_int64, [c_void_p]),
+    "hmb200_last_error": (c_char_p, []),
+    "hmb200_version": (c_char_p, []),
+}
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(f"{LIB_PATH} is not built (python -m htool_python_b200.build cuda); the engine has no fallback path")
+        _lib = ctypes.CDLL(str(LIB_PATH))
+        for name, (res, args) in EXPORTS.items():
+            fn = getattr(_lib, name)  # AttributeError if the symbol is missing
+            fn.restype, fn.argtypes = res, args
+    return _lib
+
+
+def last_error() -> str:
+    return lib().hmb200_last_error().decode()
+
+
+def check(status: int) -> None:
+    if status != 0:
+        raise RuntimeError("hmb200: " + last_error())

@@ -1,0 +1,592 @@
+// hmb200.cu -- C ABI of the engine (include/hmb200.h): create (plan + pack + upload), products, permutations.
+#include "hmb200.h"
+#include "planner.h"
+#include "../kernels/stream_kernels.cuh"
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+using namespace hmb200;
+
+static thread_local std::string g_last_error;
+
+#define CUDA_CHECK(expr)                                                                                               \
+    do {                                                                                                               \
+        cudaError_t _e = (expr);                                                                                       \
+        if (_e != cudaSuccess)                                                                                         \
+            throw std::runtime_error(std::string(#expr) + " failed: " + cudaGetErrorString(_e));                       \
+    } while (0)
+
+namespace {
+
+struct PackedOp {
+    bool valid = false;
+    char op    = 'N';
+    int32_t n_in = 0, n_out = 0;
+    uint8_t *stream[2]    = {nullptr, nullptr};
+    StageEntry *stages[2] = {nullptr, nullptr};
+    ZCopy *zcopies[2]     = {nullptr, nullptr};
+    WorkUnit *units[2]    = {nullptr, nullptr};
+    uint32_t n_units[2]   = {0, 0};
+    ReduceSeg *reduce     = nullptr;
+    uint32_t n_reduce     = 0;
+    uint64_t xz_elems     = 0;
+    // bookkeeping
+    uint64_t stream_bytes[2] = {0, 0};
+    uint64_t n_stages[2] = {0, 0}, n_pieces[2] = {0, 0};
+    uint64_t table_bytes = 0;
+    int n_bins = 0;
+};
+
+} // namespace
+
+struct hmb200_handle {
+    int device          = 0;
+    cudaStream_t stream = nullptr;
+    int es              = 8;
+    Options opt;
+    int n_sms = 0;
+    int32_t n_rows = 0, n_cols = 0;
+    PackedOp ops[3]; // N, T, C
+    void *xz = nullptr;
+    uint64_t xz_elems = 0;
+    void *ybuf = nullptr; // device staging for host-resident outputs / user-numbering paths
+    uint64_t ybuf_elems = 0;
+    void *xbuf = nullptr; // device staging for multi-RHS inputs
+    uint64_t xbuf_elems = 0;
+    void *pinned = nullptr;
+    size_t pinned_bytes = 0;
+    uint32_t *counters = nullptr; // [2]
+    int32_t *perm_t = nullptr, *perm_s = nullptr;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool timing = false;
+    float last_ms[4] = {0, 0, 0, 0};
+    int64_t launches = 0;
+    hmb200_info info{};
+};
+
+namespace {
+
+template <typename V>
+V *upload_vec(const std::vector<V> &v, cudaStream_t s) {
+    V *d = nullptr;
+    size_t bytes = std::max<size_t>(v.size() * sizeof(V), 64);
+    CUDA_CHECK(cudaMalloc(&d, bytes));
+    if (!v.empty()) CUDA_CHECK(cudaMemcpyAsync(d, v.data(), v.size() * sizeof(V), cudaMemcpyHostToDevice, s));
+    return d;
+}
+
+void ensure_pinned(hmb200_handle *h, size_t bytes) {
+    if (h->pinned_bytes >= bytes) return;
+    if (h->pinned) CUDA_CHECK(cudaFreeHost(h->pinned));
+    h->pinned = nullptr;
+    CUDA_CHECK(cudaHostAlloc(&h->pinned, bytes, cudaHostAllocDefault));
+    h->pinned_bytes = bytes;
+}
+void ensure_dev(void **p, uint64_t *have, uint64_t need_elems, int es) {
+    if (*have >= need_elems) return;
+    if (*p) CUDA_CHECK(cudaFree(*p));
+    *p = nullptr;
+    CUDA_CHECK(cudaMalloc(p, (size_t)(need_elems + 2) * es));
+    *have = need_elems;
+}
+
+// packs one phase's stream window by window through two pinned buffers and uploads it
+void upload_stream(hmb200_handle *h, const hmb200_flat &flat, const Plan &plan, int phase, uint8_t **dptr, double &pack_s, double &up_s) {
+    const PhasePlan &ph = phase == 1 ? plan.phase1 : plan.phase2;
+    CUDA_CHECK(cudaMalloc(dptr, (size_t)std::max<uint64_t>(ph.stream_bytes, 128)));
+    if (ph.stages.empty()) return;
+    const uint64_t window = std::min<uint64_t>(std::max<uint64_t>(ph.stream_bytes, 1 << 20), 256ull << 20);
+    uint8_t *buf[2] = {nullptr, nullptr};
+    cudaEvent_t done[2];
+    for (int i = 0; i < 2; i++) {
+        CUDA_CHECK(cudaHostAlloc((void **)&buf[i], (size_t)window + 256, cudaHostAllocDefault));
+        CUDA_CHECK(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+    }
+    size_t s0 = 0;
+    int k = 0;
+    const size_t ns = ph.stages.size();
+    while (s0 < ns) {
+        const uint64_t base = ph.stages[s0].gmem_off;
+        size_t s1 = s0 + 1;
+        while (s1 < ns && ph.stages[s1].gmem_off + ph.stages[s1].bytes - base <= window) s1++;
+        const uint64_t end = (s1 < ns) ? ph.stages[s1].gmem_off : ph.stream_bytes;
+        if (end - base > window + 256) throw std::runtime_error("internal: packet larger than the upload window");
+        CUDA_CHECK(cudaEventSynchronize(done[k]));
+        auto t0 = std::chrono::steady_clock::now();
+        pack_stages(flat, plan, phase, s0, s1, buf[k]);
+        auto t1 = std::chrono::steady_clock::now();
+        CUDA_CHECK(cudaMemcpyAsync(*dptr + base, buf[k], (size_t)(end - base), cudaMemcpyHostToDevice, h->stream));
+        CUDA_CHECK(cudaEventRecord(done[k], h->stream));
+        pack_s += std::chrono::duration<double>(t1 - t0).count();
+        s0 = s1;
+        k ^= 1;
+    }
+    auto t2 = std::chrono::steady_clock::now();
+    CUDA_CHECK(cudaStreamSynchronize(h->stream));
+    up_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t2).count();
+    for (int i = 0; i < 2; i++) {
+        CUDA_CHECK(cudaFreeHost(buf[i]));
+        CUDA_CHECK(cudaEventDestroy(done[i]));
+    }
+}
+
+void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) {
+    Plan plan;
+    build_plan(flat, h->es, op, h->opt, plan);
+    po.op    = op;
+    po.n_in  = plan.n_in;
+    po.n_out = plan.n_out;
+    double pack_s = 0, up_s = 0;
+    for (int ph = 0; ph < 2; ph++) {
+        const PhasePlan &pp = ph == 0 ? plan.phase1 : plan.phase2;
+        upload_stream(h, flat, plan, ph + 1, &po.stream[ph], pack_s, up_s);
+        po.stages[ph]       = upload_vec(pp.stages, h->stream);
+        po.zcopies[ph]      = upload_vec(pp.zcopies, h->stream);
+        po.units[ph]        = upload_vec(pp.units, h->stream);
+        po.n_units[ph]      = (uint32_t)pp.units.size();
+        po.stream_bytes[ph] = pp.stream_bytes;
+        po.n_stages[ph]     = pp.stages.size();
+        po.table_bytes += pp.stages.size() * sizeof(StageEntry) + pp.zcopies.size() * sizeof(ZCopy) + pp.units.size() * sizeof(WorkUnit);
+    }
+    po.n_pieces[0] = plan.pieces1.size();
+    po.n_pieces[1] = plan.pieces2.size();
+    po.reduce      = upload_vec(plan.reduce, h->stream);
+    po.n_reduce    = (uint32_t)plan.reduce.size();
+    po.table_bytes += plan.reduce.size() * sizeof(ReduceSeg);
+    po.xz_elems = plan.xz_elems;
+    po.n_bins   = (int)plan.bin_start.size() - 1;
+    CUDA_CHECK(cudaStreamSynchronize(h->stream));
+    po.valid = true;
+    if (op == 'N') {
+        h->info.stored_coefficients = plan.stored_coefficients;
+        h->info.n_bins              = po.n_bins;
+    }
+    h->info.pack_seconds += pack_s;
+    h->info.upload_seconds += up_s;
+}
+
+void free_op(PackedOp &po) {
+    for (int i = 0; i < 2; i++) {
+        cudaFree(po.stream[i]);
+        cudaFree(po.stages[i]);
+        cudaFree(po.zcopies[i]);
+        cudaFree(po.units[i]);
+    }
+    cudaFree(po.reduce);
+    po = PackedOp();
+}
+
+template <typename T>
+void set_kernel_attrs(size_t smem1, size_t smem2) {
+    CUDA_CHECK(cudaFuncSetAttribute(hmatrix_stream_kernel<T, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    CUDA_CHECK(cudaFuncSetAttribute(hmatrix_stream_kernel<T, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+}
+
+hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, const hmb200_options *opt, int es) {
+    if (!flat) throw std::runtime_error("flat is NULL");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        throw std::runtime_error("no CUDA device available (the engine has no CPU fallback)");
+    CUDA_CHECK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 9) throw std::runtime_error("device does not support bulk TMA copies (needs sm_100a)");
+    hmb200_handle *h = new hmb200_handle();
+    try {
+        h->device = device;
+        h->stream = (cudaStream_t)stream;
+        h->es     = es;
+        h->opt    = resolve_options(opt);
+        h->n_sms  = prop.multiProcessorCount;
+        h->n_rows = flat->n_rows;
+        h->n_cols = flat->n_cols;
+        // fit the ring into the opt-in shared memory of this device
+        while (h->opt.n_stages > 2 && stream_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps) > (size_t)prop.sharedMemPerBlockOptin)
+            h->opt.n_stages--;
+        h->info = hmb200_info{};
+        build_op(h, *flat, 'N', h->ops[0]);
+        if (h->opt.build_transpose) {
+            const char sym = (char)flat->symmetry_for_leaves;
+            if (sym != 'H') build_op(h, *flat, 'T', h->ops[1]);
+            if (es == 16 && sym != 'S') build_op(h, *flat, 'C', h->ops[2]);
+        }
+        for (auto &po : h->ops)
+            if (po.valid) h->xz_elems = std::max(h->xz_elems, po.xz_elems);
+        CUDA_CHECK(cudaMalloc(&h->xz, (size_t)(h->xz_elems + 4) * es));
+        CUDA_CHECK(cudaMemsetAsync(h->xz, 0, (size_t)(h->xz_elems + 4) * es, h->stream));
+        CUDA_CHECK(cudaMalloc(&h->counters, 64));
+        for (auto &ev : h->ev) CUDA_CHECK(cudaEventCreate(&ev));
+        size_t s1 = stream_smem_bytes(1, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps);
+        size_t s2 = stream_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps);
+        if (es == 8) set_kernel_attrs<double>(s1, s2); else set_kernel_attrs<double2>(s1, s2);
+        CUDA_CHECK(cudaStreamSynchronize(h->stream));
+        // info
+        const PackedOp &n = h->ops[0];
+        h->info.n_rows = h->n_rows; h->info.n_cols = h->n_cols; h->info.is_complex = es == 16;
+        h->info.n_leaves = flat->n_leaves;
+        h->info.n_pieces1 = n.n_pieces[0]; h->info.n_pieces2 = n.n_pieces[1];
+        h->info.n_stages1 = n.n_stages[0]; h->info.n_stages2 = n.n_stages[1];
+        h->info.n_reduce_segments = n.n_reduce;
+        h->info.stream1_bytes = n.stream_bytes[0]; h->info.stream2_bytes = n.stream_bytes[1];
+        h->info.table_bytes = n.table_bytes;
+        h->info.workspace_bytes = (int64_t)h->xz_elems * es;
+    } catch (...) {
+        hmb200_destroy(h);
+        throw;
+    }
+    return h;
+}
+
+} // namespace
+
+// ------------------------------------------------------------------------------------------------------------
+// product
+// ------------------------------------------------------------------------------------------------------------
+namespace {
+
+template <typename T>
+__global__ void strided_gather_kernel(const T *__restrict__ in, int n, int mu, int j, T *__restrict__ out) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = in[i * mu + j];
+}
+template <typename T>
+__global__ void strided_scatter_kernel(const T *__restrict__ in, int n, int mu, int j, T *__restrict__ out) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)n; i += (size_t)gridDim.x * blockDim.x)
+        out[i * mu + j] = in[i];
+}
+
+PackedOp &select_op(hmb200_handle *h, char trans) {
+    int idx = trans == 'N' ? 0 : (trans == 'T' ? 1 : (trans == 'C' ? (h->es == 8 ? 1 : 2) : -1));
+    if (idx < 0) throw std::runtime_error("trans must be 'N', 'T' or 'C'");
+    if (!h->ops[idx].valid)
+        throw std::runtime_error(std::string("operator for trans='") + trans + "' was not packed (create with build_transpose=1, or unsupported with this symmetry)");
+    return h->ops[idx];
+}
+
+// runs out = beta*out + alpha*op(A)*xz[0:n_in] on the handle's stream; x must already be in xz; y is a device pointer
+template <typename T>
+void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, void *y, const int32_t *out_perm) {
+    const Options &o = h->opt;
+    const int threads = (o.consumer_warps + 1) * 32;
+    const int ctas    = o.ctas > 0 ? o.ctas : h->n_sms;
+    StreamParams p{};
+    p.xz = h->xz; p.y = y; p.out_perm = out_perm;
+    p.alpha_re = alpha[0]; p.alpha_im = h->es == 16 ? alpha[1] : 0.0;
+    p.beta_re  = beta[0];  p.beta_im  = h->es == 16 ? beta[1] : 0.0;
+    p.stage_bytes = o.stage_bytes; p.z_bytes = o.stage_z_bytes; p.n_stages = o.n_stages; p.consumer_warps = o.consumer_warps;
+    CUDA_CHECK(cudaMemsetAsync(h->counters, 0, 64, h->stream));
+    if (h->timing) CUDA_CHECK(cudaEventRecord(h->ev[0], h->stream));
+    if (po.n_units[0] > 0) {
+        p.stream = po.stream[0]; p.stages = po.stages[0]; p.zcopies = po.zcopies[0]; p.units = po.units[0];
+        p.n_units = po.n_units[0]; p.counter = h->counters;
+        size_t smem = stream_smem_bytes(1, h->es, o.stage_bytes, o.stage_z_bytes, o.n_stages, o.consumer_warps);
+        hmatrix_stream_kernel<T, 1><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[0]), threads, smem, h->stream>>>(p);
+        h->launches++;
+    }
+    if (h->timing) CUDA_CHECK(cudaEventRecord(h->ev[1], h->stream));
+    if (po.n_reduce > 0) {
+        unsigned blocks = (po.n_reduce + 7) / 8;
+        reduce_partials_kernel<T><<<blocks, 256, 0, h->stream>>>(po.reduce, po.n_reduce, (T *)h->xz);
+        h->launches++;
+    }
+    if (h->timing) CUDA_CHECK(cudaEventRecord(h->ev[2], h->stream));
+    if (po.n_units[1] > 0) {
+        p.stream = po.stream[1]; p.stages = po.stages[1]; p.zcopies = po.zcopies[1]; p.units = po.units[1];
+        p.n_units = po.n_units[1]; p.counter = h->counters + 1;
+        size_t smem = stream_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_bytes, o.n_stages, o.consumer_warps);
+        hmatrix_stream_kernel<T, 2><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]), threads, smem, h->stream>>>(p);
+        h->launches++;
+    }
+    if (h->timing) CUDA_CHECK(cudaEventRecord(h->ev[3], h->stream));
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void collect_timing(hmb200_handle *h) {
+    if (!h->timing) return;
+    CUDA_CHECK(cudaEventSynchronize(h->ev[3]));
+    for (int i = 0; i < 3; i++) CUDA_CHECK(cudaEventElapsedTime(&h->last_ms[i], h->ev[i], h->ev[i + 1]));
+    CUDA_CHECK(cudaEventElapsedTime(&h->last_ms[3], h->ev[0], h->ev[3]));
+}
+
+template <typename T>
+int vector_product(hmb200_handle *h, char trans, const double *alpha, const void *in, const double *beta, void *out, int mem) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    PackedOp &po = select_op(h, trans);
+    const size_t in_b = (size_t)po.n_in * sizeof(T), out_b = (size_t)po.n_out * sizeof(T);
+    const bool beta_zero = beta[0] == 0.0 && (h->es == 8 || beta[1] == 0.0);
+    if (mem == HMB200_DEVICE) {
+        CUDA_CHECK(cudaMemcpyAsync(h->xz, in, in_b, cudaMemcpyDeviceToDevice, h->stream));
+        run_product<T>(h, po, alpha, beta, out, nullptr);
+        if (h->timing) collect_timing(h);
+    } else {
+        ensure_pinned(h, in_b + out_b + 64);
+        ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out, h->es);
+        uint8_t *pin = (uint8_t *)h->pinned, *pout = pin + ((in_b + 63) & ~(size_t)63);
+        std::memcpy(pin, in, in_b);
+        CUDA_CHECK(cudaMemcpyAsync(h->xz, pin, in_b, cudaMemcpyHostToDevice, h->stream));
+        if (!beta_zero) {
+            std::memcpy(pout, out, out_b);
+            CUDA_CHECK(cudaMemcpyAsync(h->ybuf, pout, out_b, cudaMemcpyHostToDevice, h->stream));
+        }
+        run_product<T>(h, po, alpha, beta, h->ybuf, nullptr);
+        CUDA_CHECK(cudaMemcpyAsync(pout, h->ybuf, out_b, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_CHECK(cudaStreamSynchronize(h->stream));
+        std::memcpy(out, pout, out_b);
+        collect_timing(h);
+    }
+    return 0;
+}
+
+// multi-RHS, row-major blocks.  Round-1 implementation: one streamed product per right-hand side (the factor bytes
+// are re-read mu times); the DMMA leaf-GEMM kernel that streams them once replaces this loop ("matmat").
+template <typename T>
+int matrix_product(hmb200_handle *h, char trans, const double *alpha, const void *in, const double *beta, void *out, int mu, int mem) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    if (mu <= 0) throw std::runtime_error("mu must be positive");
+    PackedOp &po = select_op(h, trans);
+    const size_t in_b = (size_t)po.n_in * mu * sizeof(T), out_b = (size_t)po.n_out * mu * sizeof(T);
+    const bool beta_zero = beta[0] == 0.0 && (h->es == 8 || beta[1] == 0.0);
+    const T *din = (const T *)in;
+    T *dout      = (T *)out;
+    uint8_t *pout = nullptr;
+    ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out * (mem == HMB200_HOST ? (mu + 1) : 1), h->es);
+    if (mem == HMB200_HOST) {
+        ensure_pinned(h, in_b + out_b + 64);
+        ensure_dev(&h->xbuf, &h->xbuf_elems, (uint64_t)po.n_in * mu, h->es);
+        uint8_t *pin = (uint8_t *)h->pinned;
+        pout         = pin + ((in_b + 63) & ~(size_t)63);
+        std::memcpy(pin, in, in_b);
+        CUDA_CHECK(cudaMemcpyAsync(h->xbuf, pin, in_b, cudaMemcpyHostToDevice, h->stream));
+        dout = (T *)h->ybuf + po.n_out; // [column scratch | row-major block]
+        if (!beta_zero) {
+            std::memcpy(pout, out, out_b);
+            CUDA_CHECK(cudaMemcpyAsync(dout, pout, out_b, cudaMemcpyHostToDevice, h->stream));
+        }
+        din = (const T *)h->xbuf;
+    }
+    T *ycol = (T *)h->ybuf;
+    const int tb = 256;
+    const unsigned gin = (unsigned)std::min<size_t>(((size_t)po.n_in + tb - 1) / tb + 1, 4096), gout = (unsigned)std::min<size_t>(((size_t)po.n_out + tb - 1) / tb + 1, 4096);
+    for (int j = 0; j < mu; j++) {
+        strided_gather_kernel<T><<<gin, tb, 0, h->stream>>>(din, po.n_in, mu, j, (T *)h->xz);
+        if (!beta_zero) strided_gather_kernel<T><<<gout, tb, 0, h->stream>>>(dout, po.n_out, mu, j, ycol);
+        run_product<T>(h, po, alpha, beta, ycol, nullptr);
+        strided_scatter_kernel<T><<<gout, tb, 0, h->stream>>>(ycol, po.n_out, mu, j, dout);
+        h->launches += beta_zero ? 2 : 3;
+    }
+    CUDA_CHECK(cudaGetLastError());
+    if (mem == HMB200_HOST) {
+        CUDA_CHECK(cudaMemcpyAsync(pout, dout, out_b, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_CHECK(cudaStreamSynchronize(h->stream));
+        std::memcpy(out, pout, out_b);
+    }
+    return 0;
+}
+
+// y_user = A x_user (alpha = 1, beta = 0) with the two permutations on the device:
+// gather (user_to_cluster) -> product -> scatter fused into the phase-2 epilogue (cluster_to_user)
+template <typename T>
+int matvec_user(hmb200_handle *h, const void *x, void *y, int mem, int mu) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    if (!h->perm_t || !h->perm_s) throw std::runtime_error("hmb200_set_permutations has not been called");
+    PackedOp &po = h->ops[0];
+    const size_t in_b = (size_t)po.n_in * mu * sizeof(T), out_b = (size_t)po.n_out * mu * sizeof(T);
+    const double one[2] = {1.0, 0.0}, zero[2] = {0.0, 0.0};
+    const T *dx = (const T *)x;
+    T *dy       = (T *)y;
+    uint8_t *pout = nullptr;
+    if (mem == HMB200_HOST) {
+        ensure_pinned(h, in_b + out_b + 64);
+        ensure_dev(&h->xbuf, &h->xbuf_elems, (uint64_t)po.n_in * mu, h->es);
+        ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out * mu, h->es);
+        uint8_t *pin = (uint8_t *)h->pinned;
+        pout         = pin + ((in_b + 63) & ~(size_t)63);
+        std::memcpy(pin, x, in_b);
+        CUDA_CHECK(cudaMemcpyAsync(h->xbuf, pin, in_b, cudaMemcpyHostToDevice, h->stream));
+        dx = (const T *)h->xbuf;
+        dy = (T *)h->ybuf;
+    }
+    const int tb = 256;
+    const unsigned gin = (unsigned)std::min<size_t>(((size_t)po.n_in + tb - 1) / tb + 1, 4096);
+    for (int j = 0; j < mu; j++) {
+        permute_gather_kernel<T><<<gin, tb, 0, h->stream>>>(h->perm_s, 0, po.n_in, dx + (size_t)j * po.n_in, (T *)h->xz, 1);
+        h->launches++;
+        run_product<T>(h, po, one, zero, dy + (size_t)j * po.n_out, h->perm_t);
+    }
+    if (mem == HMB200_HOST) {
+        CUDA_CHECK(cudaMemcpyAsync(pout, dy, out_b, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_CHECK(cudaStreamSynchronize(h->stream));
+        std::memcpy(y, pout, out_b);
+        collect_timing(h);
+    } else if (h->timing) {
+        collect_timing(h);
+    }
+    return 0;
+}
+
+template <typename F>
+int guarded(F &&f) {
+    try {
+        return f();
+    } catch (const std::exception &e) {
+        g_last_error = e.what();
+        return 1;
+    }
+}
+
+} // namespace
+
+// ------------------------------------------------------------------------------------------------------------
+// extern "C"
+// ------------------------------------------------------------------------------------------------------------
+extern "C" {
+
+hmb200_handle *hmb200_create_d(const hmb200_flat *flat, int device, void *stream, const hmb200_options *opt) {
+    try {
+        return create_impl(flat, device, stream, opt, 8);
+    } catch (const std::exception &e) {
+        g_last_error = e.what();
+        return nullptr;
+    }
+}
+hmb200_handle *hmb200_create_z(const hmb200_flat *flat, int device, void *stream, const hmb200_options *opt) {
+    try {
+        return create_impl(flat, device, stream, opt, 16);
+    } catch (const std::exception &e) {
+        g_last_error = e.what();
+        return nullptr;
+    }
+}
+
+void hmb200_destroy(hmb200_handle *h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream); else cudaDeviceSynchronize();
+    for (auto &po : h->ops) free_op(po);
+    cudaFree(h->xz);
+    cudaFree(h->ybuf);
+    cudaFree(h->xbuf);
+    cudaFree(h->counters);
+    cudaFree(h->perm_t);
+    cudaFree(h->perm_s);
+    if (h->pinned) cudaFreeHost(h->pinned);
+    for (auto &ev : h->ev)
+        if (ev) cudaEventDestroy(ev);
+    delete h;
+}
+
+int hmb200_get_info(const hmb200_handle *h, hmb200_info *info) {
+    if (!h || !info) { g_last_error = "null argument"; return 1; }
+    *info = h->info;
+    return 0;
+}
+int hmb200_set_stream(hmb200_handle *h, void *stream) {
+    if (!h) { g_last_error = "null handle"; return 1; }
+    h->stream = (cudaStream_t)stream;
+    return 0;
+}
+
+int hmb200_add_vector_product_d(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mem) {
+    return guarded([&] { if (!h || h->es != 8) throw std::runtime_error("handle is not a real (double) engine"); return vector_product<double>(h, trans, alpha, in, beta, out, mem); });
+}
+int hmb200_add_vector_product_z(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mem) {
+    return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return vector_product<double2>(h, trans, alpha, in, beta, out, mem); });
+}
+int hmb200_add_matrix_product_row_major_d(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mu, int mem) {
+    return guarded([&] { if (!h || h->es != 8) throw std::runtime_error("handle is not a real (double) engine"); return matrix_product<double>(h, trans, alpha, in, beta, out, mu, mem); });
+}
+int hmb200_add_matrix_product_row_major_z(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mu, int mem) {
+    return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return matrix_product<double2>(h, trans, alpha, in, beta, out, mu, mem); });
+}
+
+static int permute_impl(bool gather, const int32_t *perm, int off, int n, const void *in, void *out, int elem_bytes, int mu, int mem, void *stream) {
+    return guarded([&] {
+        if (elem_bytes != 8 && elem_bytes != 16) throw std::runtime_error("elem_bytes must be 8 or 16");
+        if (n < 0 || mu < 0) throw std::runtime_error("negative size");
+        if (n == 0 || mu == 0) return 0;
+        cudaStream_t s = (cudaStream_t)stream;
+        const size_t bytes = (size_t)n * mu * elem_bytes;
+        const int32_t *dperm = perm;
+        const void *din = in;
+        void *dout = out;
+        int32_t *tp = nullptr; void *ti = nullptr, *to = nullptr;
+        if (mem == HMB200_HOST) {
+            CUDA_CHECK(cudaMalloc(&tp, sizeof(int32_t) * (size_t)(off + n)));
+            CUDA_CHECK(cudaMalloc(&ti, bytes));
+            CUDA_CHECK(cudaMalloc(&to, bytes));
+            CUDA_CHECK(cudaMemcpyAsync(tp, perm, sizeof(int32_t) * (size_t)(off + n), cudaMemcpyHostToDevice, s));
+            CUDA_CHECK(cudaMemcpyAsync(ti, in, bytes, cudaMemcpyHostToDevice, s));
+            dperm = tp; din = ti; dout = to;
+        }
+        const int tb = 256;
+        const unsigned g = (unsigned)std::min<size_t>(((size_t)n * mu + tb - 1) / tb, 148 * 16);
+        if (elem_bytes == 8) {
+            if (gather) permute_gather_kernel<double><<<g, tb, 0, s>>>(dperm, off, n, (const double *)din, (double *)dout, mu);
+            else permute_scatter_kernel<double><<<g, tb, 0, s>>>(dperm, off, n, (const double *)din, (double *)dout, mu);
+        } else {
+            if (gather) permute_gather_kernel<double2><<<g, tb, 0, s>>>(dperm, off, n, (const double2 *)din, (double2 *)dout, mu);
+            else permute_scatter_kernel<double2><<<g, tb, 0, s>>>(dperm, off, n, (const double2 *)din, (double2 *)dout, mu);
+        }
+        CUDA_CHECK(cudaGetLastError());
+        if (mem == HMB200_HOST) {
+            CUDA_CHECK(cudaMemcpyAsync(out, to, bytes, cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaStreamSynchronize(s));
+            cudaFree(tp); cudaFree(ti); cudaFree(to);
+        }
+        return 0;
+    });
+}
+int hmb200_permute_gather(const int32_t *perm, int off, int n, const void *in, void *out, int elem_bytes, int mu, int mem, void *stream) {
+    return permute_impl(true, perm, off, n, in, out, elem_bytes, mu, mem, stream);
+}
+int hmb200_permute_scatter(const int32_t *perm, int off, int n, const void *in, void *out, int elem_bytes, int mu, int mem, void *stream) {
+    return permute_impl(false, perm, off, n, in, out, elem_bytes, mu, mem, stream);
+}
+
+int hmb200_set_permutations(hmb200_handle *h, const int32_t *target_perm_local, const int32_t *source_perm_local) {
+    return guarded([&] {
+        if (!h || !target_perm_local || !source_perm_local) throw std::runtime_error("null argument");
+        CUDA_CHECK(cudaSetDevice(h->device));
+        if (!h->perm_t) CUDA_CHECK(cudaMalloc(&h->perm_t, sizeof(int32_t) * (size_t)std::max(h->n_rows, 1)));
+        if (!h->perm_s) CUDA_CHECK(cudaMalloc(&h->perm_s, sizeof(int32_t) * (size_t)std::max(h->n_cols, 1)));
+        CUDA_CHECK(cudaMemcpyAsync(h->perm_t, target_perm_local, sizeof(int32_t) * (size_t)h->n_rows, cudaMemcpyHostToDevice, h->stream));
+        CUDA_CHECK(cudaMemcpyAsync(h->perm_s, source_perm_local, sizeof(int32_t) * (size_t)h->n_cols, cudaMemcpyHostToDevice, h->stream));
+        CUDA_CHECK(cudaStreamSynchronize(h->stream));
+        return 0;
+    });
+}
+int hmb200_matvec_user_d(hmb200_handle *h, const double *x, double *y, int mem) {
+    return guarded([&] { if (!h || h->es != 8) throw std::runtime_error("handle is not a real (double) engine"); return matvec_user<double>(h, x, y, mem, 1); });
+}
+int hmb200_matvec_user_z(hmb200_handle *h, const double *x, double *y, int mem) {
+    return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return matvec_user<double2>(h, x, y, mem, 1); });
+}
+int hmb200_matmat_user_d(hmb200_handle *h, const double *X, double *Y, int mu, int mem) {
+    return guarded([&] { if (!h || h->es != 8) throw std::runtime_error("handle is not a real (double) engine"); return matvec_user<double>(h, X, Y, mem, mu); });
+}
+int hmb200_matmat_user_z(hmb200_handle *h, const double *X, double *Y, int mu, int mem) {
+    return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return matvec_user<double2>(h, X, Y, mem, mu); });
+}
+
+int hmb200_last_kernel_ms(hmb200_handle *h, float ms[4]) {
+    if (!h || !ms) { g_last_error = "null argument"; return 1; }
+    for (int i = 0; i < 4; i++) ms[i] = h->last_ms[i];
+    return 0;
+}
+int hmb200_enable_timing(hmb200_handle *h, int on) {
+    if (!h) { g_last_error = "null handle"; return 1; }
+    h->timing = on != 0;
+    return 0;
+}
+int64_t hmb200_launch_count(const hmb200_handle *h) { return h ? h->launches : 0; }
+
+const char *hmb200_last_error(void) { return g_last_error.c_str(); }
+const char *hmb200_version(void) { return "hmb200 0.1 (sm_100a)"; }
+
+} // extern "C"

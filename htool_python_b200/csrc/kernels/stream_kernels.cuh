@@ -1,0 +1,264 @@
+// stream_kernels.cuh -- the two streaming phases of the H-matrix product as ONE persistent, warp-specialised kernel
+// template (sm_100a):
+//
+//   PHASE 1:  t_j = V_j x[cols_j]            for every low-rank leaf j   (reference: first gemv of
+//             lib/htool/include/htool/hmatrix/lrmat/linalg/add_lrmat_vector_product.hpp:15-16)
+//   PHASE 2:  y[bin] = beta y[bin] + alpha (sum_j U_j[bin rows] t_j + sum_d D_d[bin rows] x[cols_d])
+//             (second gemv :17 and the dense gemv of matrix/linalg/add_matrix_vector_product.hpp:10-23; the leaf loop
+//             and its reduction are hmatrix/linalg/add_hmatrix_vector_product.hpp:90-103 / :139-169)
+//
+// One CTA per SM.  Warp `NW` is the producer: it claims work units (a target bin in phase 2, a run of packets in
+// phase 1) from a global counter and streams their packets through a ring of shared-memory stages with 1-D bulk TMA
+// copies (cp.async.bulk, one per packet + one small one per tile for the operand slice), signalling mbarriers.
+// Warps 0..NW-1 consume: each tile of a packet is taken by one warp (round robin), lanes own output rows, the
+// per-bin cross-warp reduction goes through shared memory, and exactly one CTA writes each output row: no atomics.
+// The kernel is HBM-bound by design: 1 FMA per 8 (16) bytes streamed.
+#pragma once
+#include "../capi/plan.h"
+#include "ptx.cuh"
+#include "scalar.cuh"
+
+namespace hmb200 {
+
+struct StreamParams {
+    const uint8_t *stream;
+    const StageEntry *stages;
+    const ZCopy *zcopies;
+    const WorkUnit *units;
+    uint32_t n_units;
+    uint32_t *counter;
+    void *xz;               // T*: x | t | partials
+    void *y;                // T*: phase-2 output (cluster numbering, or user numbering when out_perm != nullptr)
+    const int32_t *out_perm; // optional fused cluster_to_user scatter: y[out_perm[row]] (perm already made local)
+    double alpha_re, alpha_im, beta_re, beta_im;
+    int stage_bytes, z_bytes, n_stages, consumer_warps;
+};
+
+constexpr int kBarrierBytes = 256;
+
+__host__ __device__ inline size_t stream_smem_bytes(int phase, int elem_bytes, int stage_bytes, int z_bytes, int n_stages, int consumer_warps) {
+    size_t red = phase == 2 ? (size_t)2 * consumer_warps * kMaxBinRows * elem_bytes : 0;
+    return kBarrierBytes + red + (size_t)n_stages * (stage_bytes + z_bytes);
+}
+
+template <typename T, int PHASE>
+__global__ void __launch_bounds__(17 * 32, 1) hmatrix_stream_kernel(const StreamParams p) {
+    using S = Scalar<T>;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int NW   = p.consumer_warps;
+    const int NS   = p.n_stages;
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    const uint32_t bar_base  = ptx::smem_u32(smem);
+    const size_t red_bytes   = PHASE == 2 ? (size_t)2 * NW * kMaxBinRows * sizeof(T) : 0;
+    uint8_t *stage_base      = smem + kBarrierBytes + red_bytes;
+    const uint32_t stage_sz  = (uint32_t)(p.stage_bytes + p.z_bytes);
+    auto full_bar  = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (NS + s); };
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; s++) {
+            ptx::mbar_init(full_bar(s), 1);
+            ptx::mbar_init(empty_bar(s), NW);
+        }
+        ptx::fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (warp == NW) {
+        // ============================== producer warp ==============================
+        const uint64_t pol_stream = ptx::policy_evict_first(); // factor bytes are read exactly once
+        const uint64_t pol_vec    = ptx::policy_evict_last();  // x / t slices are re-read by many tiles: keep in L2
+        const T *xz = (const T *)p.xz;
+        uint32_t it = 0;
+        while (true) {
+            uint32_t u = 0;
+            if (lane == 0) u = atomicAdd(p.counter, 1u);
+            u = __shfl_sync(0xffffffffu, u, 0);
+            if (u >= p.n_units) break;
+            const WorkUnit wu = p.units[u];
+            for (uint32_t s = wu.first_stage; s < wu.first_stage + wu.n_stages; s++, it++) {
+                const uint4 e0 = __ldg(reinterpret_cast<const uint4 *>(p.stages + s));
+                const uint4 e1 = __ldg(reinterpret_cast<const uint4 *>(p.stages + s) + 1);
+                const uint64_t gmem_off = (uint64_t)e0.x | ((uint64_t)e0.y << 32);
+                const uint32_t bytes = e0.z, z_first = e0.w, n_z = e1.x, z_bytes = e1.y;
+                uint2 zc = make_uint2(0, 0);
+                if ((uint32_t)lane < n_z) zc = __ldg(reinterpret_cast<const uint2 *>(p.zcopies + z_first) + lane);
+                const int slot       = it % NS;
+                const uint32_t par   = (it / NS) & 1u;
+                const uint32_t sbase = ptx::smem_u32(stage_base + (size_t)slot * stage_sz);
+                ptx::mbar_wait(empty_bar(slot), par ^ 1u);
+                if (lane == 0) {
+                    ptx::mbar_arrive_expect_tx(full_bar(slot), bytes + z_bytes);
+                    ptx::bulk_g2s(sbase, p.stream + gmem_off, bytes, full_bar(slot), pol_stream);
+                }
+                __syncwarp();
+                for (uint32_t i = lane; i < n_z; i += 32) {
+                    if (i >= 32) zc = __ldg(reinterpret_cast<const uint2 *>(p.zcopies + z_first) + i);
+                    const uint32_t zb = zc.y & 0xffffu, zdst = zc.y >> 16;
+                    ptx::bulk_g2s(sbase + p.stage_bytes + zdst, xz + zc.x, zb, full_bar(slot), pol_vec);
+                }
+            }
+        }
+        // terminate packet: a header written through the generic proxy, released by a plain arrive
+        {
+            const int slot     = it % NS;
+            const uint32_t par = (it / NS) & 1u;
+            ptx::mbar_wait(empty_bar(slot), par ^ 1u);
+            if (lane == 0) {
+                PacketHeader *h = reinterpret_cast<PacketHeader *>(stage_base + (size_t)slot * stage_sz);
+                h->n_pieces = 0;
+                h->flags    = (uint16_t)kFlagTerminate;
+                ptx::mbar_arrive(full_bar(slot));
+            }
+        }
+        return;
+    }
+    if (warp > NW) return;
+
+    // ============================== consumer warps ==============================
+    T *xz = (T *)p.xz;
+    T acc0 = S::zero(), acc1 = S::zero();
+    int bin_parity = 0;
+    for (uint32_t it = 0;; it++) {
+        const int slot     = it % NS;
+        const uint32_t par = (it / NS) & 1u;
+        ptx::mbar_wait(full_bar(slot), par);
+        const uint8_t *pk       = stage_base + (size_t)slot * stage_sz;
+        const uint4 hraw        = *reinterpret_cast<const uint4 *>(pk);
+        const uint32_t n_pieces = hraw.x, piece_base = hraw.y, row0 = hraw.z;
+        const uint32_t bin_rows = hraw.w & 0xffffu, flags = hraw.w >> 16;
+        if (flags & kFlagTerminate) break;
+        const T *zarea = reinterpret_cast<const T *>(pk + p.stage_bytes);
+
+        int first = (int)((NW - (piece_base % NW) + warp) % NW); // pieces with (piece_base + i) % NW == warp
+        for (uint32_t i = first; i < n_pieces; i += NW) {
+            const uint4 d       = *reinterpret_cast<const uint4 *>(pk + 16 + 16 * i);
+            const T *A          = reinterpret_cast<const T *>(pk + d.x);
+            const T *z          = zarea + (d.z & 0xffffu);
+            const int nc        = (int)(d.z >> 16);
+            const int nr        = (int)(d.w & 0xffu);
+            if (PHASE == 2) {
+                const int ro  = (int)((d.w >> 8) & 0xffu);
+                const int i0  = lane - ro, i1 = lane + 32 - ro;
+                const bool a0 = (unsigned)i0 < (unsigned)nr, a1 = (unsigned)i1 < (unsigned)nr;
+                const T *p0   = A + (a0 ? i0 : 0);
+                const T *p1   = A + (a1 ? i1 : 0);
+                T b0 = S::zero(), b1 = S::zero(); // second accumulator pair for ILP
+                int c = 0;
+                for (; c + 2 <= nc; c += 2) {
+                    const T z0 = z[c], z1 = z[c + 1];
+                    const T v00 = a0 ? p0[(size_t)c * nr] : S::zero();
+                    const T v10 = a1 ? p1[(size_t)c * nr] : S::zero();
+                    const T v01 = a0 ? p0[(size_t)(c + 1) * nr] : S::zero();
+                    const T v11 = a1 ? p1[(size_t)(c + 1) * nr] : S::zero();
+                    S::fma(acc0, v00, z0);
+                    S::fma(acc1, v10, z0);
+                    S::fma(b0, v01, z1);
+                    S::fma(b1, v11, z1);
+                }
+                if (c < nc) {
+                    const T z0 = z[c];
+                    const T v00 = a0 ? p0[(size_t)c * nr] : S::zero();
+                    const T v10 = a1 ? p1[(size_t)c * nr] : S::zero();
+                    S::fma(acc0, v00, z0);
+                    S::fma(acc1, v10, z0);
+                }
+                acc0 = S::add(acc0, b0);
+                acc1 = S::add(acc1, b1);
+            } else {
+                // tile lr x nq (ld lr): lane -> (row l = lane % lr, column group g = lane / lr)
+                const int lr = nr, nq = nc;
+                const int G  = 32 / lr;
+                const int l  = lane % lr, g = lane / lr;
+                T s0 = S::zero(), s1 = S::zero();
+                if (g < G) {
+                    const T *pv = A + l;
+                    int k = g;
+                    for (; k + G < nq; k += 2 * G) {
+                        S::fma(s0, pv[(size_t)k * lr], z[k]);
+                        S::fma(s1, pv[(size_t)(k + G) * lr], z[k + G]);
+                    }
+                    if (k < nq) S::fma(s0, pv[(size_t)k * lr], z[k]);
+                }
+                s0 = S::add(s0, s1);
+                for (int gg = 1; gg < G; gg++) {
+                    const T o = S::shfl(s0, lane < lr ? lane + gg * lr : lane);
+                    if (lane < lr) s0 = S::add(s0, o);
+                }
+                if (lane < lr) xz[d.y + lane] = s0;
+            }
+        }
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(empty_bar(slot));
+
+        if (PHASE == 2 && (flags & kFlagLastOfBin)) {
+            T *red = reinterpret_cast<T *>(smem + kBarrierBytes) + (size_t)bin_parity * NW * kMaxBinRows;
+            red[warp * kMaxBinRows + lane]      = acc0;
+            red[warp * kMaxBinRows + 32 + lane] = acc1;
+            ptx::named_bar_sync(1, NW * 32);
+            const uint32_t tid = threadIdx.x;
+            if (tid < bin_rows) {
+                T s = red[tid];
+                for (int w = 1; w < NW; w++) s = S::add(s, red[w * kMaxBinRows + tid]);
+                const T alpha = S::make(p.alpha_re, p.alpha_im), beta = S::make(p.beta_re, p.beta_im);
+                T *y = (T *)p.y;
+                const size_t o = p.out_perm ? (size_t)p.out_perm[row0 + tid] : (size_t)(row0 + tid);
+                T r = S::mul(alpha, s);
+                if (!S::is_zero(beta)) r = S::add(r, S::mul(beta, y[o])); // beta == 0 must not propagate NaNs of y (BLAS)
+                y[o] = r;
+            }
+            acc0 = S::zero();
+            acc1 = S::zero();
+            bin_parity ^= 1;
+        }
+    }
+}
+
+// t[final + l] = sum_q partial[first + q*len + l]   (one warp per segment; deterministic order)
+template <typename T>
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const ReduceSeg *segs, uint32_t n_segs, T *xz) {
+    using S = Scalar<T>;
+    const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane   = threadIdx.x & 31;
+    if (w >= n_segs) return;
+    const uint4 sg = __ldg(reinterpret_cast<const uint4 *>(segs + w));
+    const int len = (int)sg.w, G = 32 / len, l = lane % len, g = lane / len;
+    T s0 = S::zero(), s1 = S::zero();
+    if (g < G) {
+        const T *pp = xz + sg.y + l;
+        uint32_t q = g;
+        for (; q + G < sg.z; q += 2 * G) {
+            s0 = S::add(s0, pp[(size_t)q * len]);
+            s1 = S::add(s1, pp[(size_t)(q + G) * len]);
+        }
+        if (q < sg.z) s0 = S::add(s0, pp[(size_t)q * len]);
+    }
+    s0 = S::add(s0, s1);
+    for (int gg = 1; gg < G; gg++) {
+        const T o = S::shfl(s0, lane < len ? lane + gg * len : lane);
+        if (lane < len) s0 = S::add(s0, o);
+    }
+    if (lane < len) xz[sg.x + lane] = s0;
+}
+
+// permutations (bit-exact data movement; clustering/cluster_node.hpp:149-175)
+template <typename T>
+__global__ void permute_gather_kernel(const int32_t *__restrict__ perm, int off, int n, const T *__restrict__ in, T *__restrict__ out, int mu) {
+    const size_t total = (size_t)n * mu;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const size_t c = t / n, i = t - c * n;
+        out[t] = in[c * n + (size_t)(perm[off + i] - off)];
+    }
+}
+template <typename T>
+__global__ void permute_scatter_kernel(const int32_t *__restrict__ perm, int off, int n, const T *__restrict__ in, T *__restrict__ out, int mu) {
+    const size_t total = (size_t)n * mu;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const size_t c = t / n, i = t - c * n;
+        out[c * n + (size_t)(perm[off + i] - off)] = in[t];
+    }
+}
+
+} // namespace hmb200

@@ -1,0 +1,142 @@
+/*
+ * hmb200.h -- C ABI of the B200-native H-matrix product engine (libhmb200.so).
+ *
+ * Drop-in boundary for ONE path of htool-ddm/htool_python: y += A*x / Y += A*X on an assembled htool::HMatrix and the
+ * block-row DistributedOperator product built on it.  Plain pointers and sizes only; no torch / pybind types.
+ * Every entry point cites the reference interface it replaces (paths relative to /root/reference; `core/` is
+ * lib/htool/include/htool/).  INTEGRATION.md shows the reference-side bindings (pybind11 operator subclass / ctypes).
+ *
+ * Conventions (identical to the reference's operator interface,
+ * core/distributed_operator/interfaces/virtual_global_to_local_operator.hpp:8-35):
+ *   out = beta*out + alpha*op(A)*in, vectors in CLUSTER numbering, multi-RHS blocks row-major (row i, rhs j at i*mu+j).
+ *   Scalars are passed by pointer (double for _d, two doubles re,im for _z) so the ABI has no complex type.
+ *   `mem` says where in/out live: HMB200_HOST (copied through pinned staging, synchronous on return, like the
+ *   reference which owns host buffers) or HMB200_DEVICE (device pointers on `stream`, asynchronous).
+ *   All functions return 0 on success, non-zero on error; hmb200_last_error() returns the message (thread-local).
+ *   There is no CPU fallback: if no CUDA device is usable, create fails.
+ */
+#ifndef HMB200_H
+#define HMB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HMB200_HOST 0
+#define HMB200_DEVICE 1
+
+/* leaf flags */
+#define HMB200_LEAF_MIRROR 1u                       /* leaf is also in leaves_for_symmetry (core/hmatrix/hmatrix.hpp:262-266) */
+#define HMB200_LEAF_DENSE_KIND(f) (((f) >> 1) & 7u) /* 0 general, 1 'S'/'L', 2 'S'/'U', 3 'H'/'L', 4 'H'/'U' */
+
+/*
+ * Flat leaf table of an assembled htool::HMatrix block (what get_leaves_from enumerates, core/hmatrix/hmatrix.hpp:247-274,
+ * addressed as in core/hmatrix/linalg/add_hmatrix_vector_product.hpp:90-103).  All pointers are HOST pointers that stay
+ * owned by the caller (they point straight into the reference's Matrix / LowRankMatrix buffers); they are only read
+ * during hmb200_create_*.
+ */
+typedef struct hmb200_flat {
+    int32_t n_rows, n_cols;      /* size of the root block (target x source cluster) */
+    int64_t n_leaves;
+    const int32_t *row_off;      /* leaf target offset - root target offset */
+    const int32_t *col_off;      /* leaf source offset - root source offset */
+    const int32_t *nrows;        /* leaf target size */
+    const int32_t *ncols;        /* leaf source size */
+    const int32_t *rank;         /* -1 dense (core/hmatrix/hmatrix.hpp:142-144), >= 0 low-rank */
+    const uint8_t *flags;        /* HMB200_LEAF_* */
+    const void *const *a;        /* dense: nrows x ncols col-major (ld nrows); low-rank: U nrows x rank col-major */
+    const void *const *b;        /* low-rank: V rank x ncols col-major (ld rank) (core/hmatrix/lrmat/lrmat.hpp:47-50) */
+    int32_t symmetry_for_leaves; /* 'N', 'S' or 'H' (HMatrix::get_symmetry_for_leaves) */
+    int32_t n_row_cuts;          /* optional: target leaf-cluster boundaries (0 ... n_rows), may be 0 / NULL */
+    const int32_t *row_cuts;
+} hmb200_flat;
+
+/* tuning knobs; zero / NULL means default */
+typedef struct hmb200_options {
+    int32_t stage_bytes;     /* bytes of one staged packet in shared memory (default 32768) */
+    int32_t stage_z_bytes;   /* bytes of the per-stage operand (x / t) area (default 8192) */
+    int32_t n_stages;        /* depth of the TMA ring (default 5) */
+    int32_t consumer_warps;  /* consumer warps per CTA (default 8) */
+    int32_t piece1_bytes;    /* target bytes of a phase-1 (V) piece (default 8192) */
+    int32_t piece2_bytes;    /* max bytes of a phase-2 (U / dense) piece (default 8192) */
+    int32_t bin_rows;        /* max rows of a target bin, <= 64 (default 64) */
+    int32_t unit_stages;     /* phase-1 stages per work unit (default 32) */
+    int32_t ctas;            /* persistent CTAs (default: number of SMs) */
+    int32_t build_transpose; /* also pack the transposed operator so trans='T'/'C' products work (default 0) */
+    int32_t reserved[6];
+} hmb200_options;
+
+typedef struct hmb200_handle hmb200_handle;
+
+/* information about a created engine */
+typedef struct hmb200_info {
+    int32_t n_rows, n_cols;
+    int32_t is_complex;
+    int32_t n_bins;
+    int64_t n_leaves, n_pieces1, n_pieces2, n_stages1, n_stages2, n_reduce_segments;
+    int64_t stream1_bytes, stream2_bytes; /* packed bytes streamed per product by phase 1 / phase 2 */
+    int64_t table_bytes;                  /* stage / operand-copy / unit tables */
+    int64_t workspace_bytes;              /* x | t | partial workspace */
+    double stored_coefficients;           /* W = sum r(m+n) + sum m n, mirrored leaves counted once,
+                                             symmetric dense leaves m(n+1)/2 (core/hmatrix/hmatrix_output.hpp:153-208) */
+    double pack_seconds, upload_seconds;
+} hmb200_info;
+
+/* ---- life cycle ------------------------------------------------------------------------------------------------
+ * Replaces: the per-call leaf enumeration of the reference (get_leaves_from is re-run by every product,
+ * core/hmatrix/linalg/add_hmatrix_vector_product.hpp:72) by a one-time flatten + pack + upload. */
+hmb200_handle *hmb200_create_d(const hmb200_flat *flat, int device, void *stream, const hmb200_options *opt);
+hmb200_handle *hmb200_create_z(const hmb200_flat *flat, int device, void *stream, const hmb200_options *opt);
+void hmb200_destroy(hmb200_handle *h);
+int hmb200_get_info(const hmb200_handle *h, hmb200_info *info);
+int hmb200_set_stream(hmb200_handle *h, void *stream);
+
+/* ---- products (cluster numbering) ------------------------------------------------------------------------------
+ * Replaces VirtualGlobalToLocalOperator::add_vector_product
+ *   (core/distributed_operator/interfaces/virtual_global_to_local_operator.hpp:16) as implemented by
+ *   RestrictedGlobalToLocalHMatrix -> openmp_internal_add_hmatrix_vector_product
+ *   (core/distributed_operator/implementations/global_to_local_operators/hmatrix.hpp:27-29,
+ *    core/hmatrix/linalg/add_hmatrix_vector_product.hpp:106-170). */
+int hmb200_add_vector_product_d(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mem);
+int hmb200_add_vector_product_z(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mem);
+
+/* Replaces VirtualGlobalToLocalOperator::add_matrix_product_row_major (same header :25) ->
+ *   openmp_internal_add_hmatrix_matrix_product_row_major (core/hmatrix/linalg/add_hmatrix_matrix_product_row_major.hpp:111-178). */
+int hmb200_add_matrix_product_row_major_d(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mu, int mem);
+int hmb200_add_matrix_product_row_major_z(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mu, int mem);
+
+/* ---- permutations (bit-exact) -----------------------------------------------------------------------------------
+ * gather : out[i] = in[perm[off+i]-off]   user_to_cluster / global_to_root_cluster (core/clustering/cluster_node.hpp:110-119,162-175)
+ * scatter: out[perm[off+i]-off] = in[i]   cluster_to_user / root_cluster_to_global (core/clustering/cluster_node.hpp:99-109,149-161)
+ * `perm` follows `mem` like in/out; `elem_bytes` is 8 (double) or 16 (complex<double>); `mu` columns of length n stored
+ * one after the other (column-major block, as add_hmatrix_matrix_product permutes per column,
+ * core/hmatrix/linalg/add_hmatrix_matrix_product.hpp:190-204). */
+int hmb200_permute_gather(const int32_t *perm, int off, int n, const void *in, void *out, int elem_bytes, int mu, int mem, void *stream);
+int hmb200_permute_scatter(const int32_t *perm, int off, int n, const void *in, void *out, int elem_bytes, int mu, int mem, void *stream);
+
+/* ---- user-numbering convenience (what HMatrix.__mul__ / __matmul__ do, src/htool/hmatrix/hmatrix.hpp:101-138):
+ * y = A x with both permutations fused into the device pipeline.  x, y: user numbering; X, Y column-major n x mu
+ * (the Fortran-ordered arrays of the Python API).  perms are device-resident after hmb200_set_permutations. */
+int hmb200_set_permutations(hmb200_handle *h, const int32_t *target_perm_local, const int32_t *source_perm_local);
+int hmb200_matvec_user_d(hmb200_handle *h, const double *x, double *y, int mem);
+int hmb200_matvec_user_z(hmb200_handle *h, const double *x, double *y, int mem);
+int hmb200_matmat_user_d(hmb200_handle *h, const double *X, double *Y, int mu, int mem);
+int hmb200_matmat_user_z(hmb200_handle *h, const double *X, double *Y, int mu, int mem);
+
+/* timing of the kernels of the last product on the handle's stream (CUDA events), in milliseconds:
+ * ms[0] phase 1 (t = V x), ms[1] partial reduce, ms[2] phase 2 (y += U t, y += D x), ms[3] whole product */
+int hmb200_last_kernel_ms(hmb200_handle *h, float ms[4]);
+int hmb200_enable_timing(hmb200_handle *h, int on);
+/* number of kernel launches issued by this handle since creation */
+int64_t hmb200_launch_count(const hmb200_handle *h);
+
+const char *hmb200_last_error(void);
+const char *hmb200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HMB200_H */

@@ -1,0 +1,121 @@
+// tests/native/plan_emulator.cpp -- TEST-ONLY host interpreter of the packed packet streams.
+//
+// Runs the planner + packer of the product library (htool_python_b200/csrc/capi/planner.cpp) and then walks the packed
+// bytes exactly as the CUDA kernel does (packet header -> piece descriptors -> tiles, operand slices fetched through
+// the ZCopy table into a stage-local area, per-piece partials, reduce segments, per-bin accumulation), on the CPU.
+// It lets the CPU test-suite (-m "not gpu") validate the schedule and the packed layout against the oracle without a
+// GPU.  It is NOT part of libhmb200.so and is never used by the product path.
+#include "planner.h"
+
+#include <complex>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+using namespace hmb200;
+
+template <typename T>
+static void emulate(const hmb200_flat &flat, char op, const Options &opt, T alpha, const T *in, T beta, T *out, int64_t *stats) {
+    const int es = sizeof(T);
+    Plan plan;
+    build_plan(flat, es, op, opt, plan);
+    std::vector<T> xz(plan.xz_elems + 4, T(0));
+    std::copy(in, in + plan.n_in, xz.begin());
+    std::vector<uint8_t> zarea(opt.stage_z_bytes);
+    for (int phase = 1; phase <= 2; phase++) {
+        const PhasePlan &ph = phase == 1 ? plan.phase1 : plan.phase2;
+        std::vector<uint8_t> stream(ph.stream_bytes + 256, 0xAB);
+        if (!ph.stages.empty()) pack_stages(flat, plan, phase, 0, ph.stages.size(), stream.data());
+        if (phase == 2) { // between the phases: the partial reduction kernel
+            for (const ReduceSeg &rs : plan.reduce)
+                for (uint32_t l = 0; l < rs.len; l++) {
+                    T s = 0;
+                    for (uint32_t q = 0; q < rs.n_parts; q++) s += xz[rs.first_partial + (size_t)q * rs.len + l];
+                    xz[rs.final_off + l] = s;
+                }
+        }
+        std::vector<char> row_written(plan.n_out, 0);
+        for (const WorkUnit &wu : ph.units) {
+            T acc[kMaxBinRows];
+            for (auto &a : acc) a = T(0);
+            for (uint32_t s = wu.first_stage; s < wu.first_stage + wu.n_stages; s++) {
+                const StageEntry &se = ph.stages[s];
+                if (se.bytes > (uint32_t)opt.stage_bytes || (se.bytes & 15) || (se.gmem_off & 15)) throw std::runtime_error("bad packet size/alignment");
+                if (se.z_bytes > (uint32_t)opt.stage_z_bytes) throw std::runtime_error("z-area overflow");
+                const uint8_t *pk = stream.data() + se.gmem_off;
+                std::memset(zarea.data(), 0xCD, zarea.size());
+                uint32_t zsum = 0;
+                for (uint32_t i = 0; i < se.n_z; i++) {
+                    const ZCopy &zc = ph.zcopies[se.z_first + i];
+                    if ((zc.bytes & 15) || (zc.dst_off & 15) || (((size_t)zc.src_elem * es) & 15)) throw std::runtime_error("misaligned operand copy");
+                    if ((size_t)zc.src_elem * es + zc.bytes > xz.size() * es) throw std::runtime_error("operand copy out of bounds");
+                    if ((uint32_t)zc.dst_off + zc.bytes > (uint32_t)opt.stage_z_bytes) throw std::runtime_error("operand copy overflows the z-area");
+                    std::memcpy(zarea.data() + zc.dst_off, (const uint8_t *)xz.data() + (size_t)zc.src_elem * es, zc.bytes);
+                    zsum += zc.bytes;
+                }
+                if (zsum != se.z_bytes) throw std::runtime_error("z_bytes mismatch");
+                PacketHeader h;
+                std::memcpy(&h, pk, 16);
+                const T *z_base = (const T *)zarea.data();
+                for (uint32_t i = 0; i < h.n_pieces; i++) {
+                    PieceDesc d;
+                    std::memcpy(&d, pk + 16 + 16 * (size_t)i, 16);
+                    if (d.data_off & 15) throw std::runtime_error("misaligned tile");
+                    const T *A = (const T *)(pk + d.data_off);
+                    const T *z = z_base + d.z_off;
+                    if (d.data_off + (size_t)d.nr * d.nc * es > se.bytes) throw std::runtime_error("tile exceeds packet");
+                    if (phase == 1) {
+                        if (d.nr > kMaxPhase1Rows) throw std::runtime_error("phase-1 tile too tall");
+                        for (int l = 0; l < d.nr; l++) {
+                            T s = 0;
+                            for (int k = 0; k < d.nc; k++) s += A[(size_t)k * d.nr + l] * z[k];
+                            xz[d.out_off + l] = s;
+                        }
+                    } else {
+                        if (d.ro + d.nr > h.bin_rows) throw std::runtime_error("tile exceeds bin");
+                        for (int c = 0; c < d.nc; c++)
+                            for (int i2 = 0; i2 < d.nr; i2++) acc[d.ro + i2] += A[(size_t)c * d.nr + i2] * z[c];
+                    }
+                }
+                if (phase == 2 && (h.flags & kFlagLastOfBin)) {
+                    for (int r = 0; r < h.bin_rows; r++) {
+                        T v = alpha * acc[r];
+                        if (beta != T(0)) v += beta * out[h.row0 + r];
+                        out[h.row0 + r] = v;
+                        if (row_written[h.row0 + r]) throw std::runtime_error("output row written twice");
+                        row_written[h.row0 + r] = 1;
+                    }
+                    for (auto &a : acc) a = T(0);
+                }
+            }
+        }
+        if (phase == 2)
+            for (int r = 0; r < plan.n_out; r++)
+                if (!row_written[r]) throw std::runtime_error("output row " + std::to_string(r) + " never written");
+    }
+    if (stats) {
+        stats[0] = (int64_t)plan.phase1.stream_bytes; stats[1] = (int64_t)plan.phase2.stream_bytes;
+        stats[2] = (int64_t)plan.pieces1.size(); stats[3] = (int64_t)plan.pieces2.size();
+        stats[4] = (int64_t)plan.phase1.stages.size(); stats[5] = (int64_t)plan.phase2.stages.size();
+        stats[6] = (int64_t)plan.reduce.size(); stats[7] = (int64_t)plan.bin_start.size() - 1;
+        stats[8] = (int64_t)plan.xz_elems; stats[9] = (int64_t)plan.stored_coefficients;
+    }
+}
+
+static thread_local std::string g_err;
+
+extern "C" int plan_emulate(const hmb200_flat *flat, int elem_bytes, char op, const hmb200_options *opt, const double *alpha, const void *in, const double *beta, void *out, int64_t *stats) {
+    try {
+        Options o = resolve_options(opt);
+        if (elem_bytes == 8)
+            emulate<double>(*flat, op, o, alpha[0], (const double *)in, beta[0], (double *)out, stats);
+        else
+            emulate<std::complex<double>>(*flat, op, o, {alpha[0], alpha[1]}, (const std::complex<double> *)in, {beta[0], beta[1]}, (std::complex<double> *)out, stats);
+        return 0;
+    } catch (const std::exception &e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+extern "C" const char *plan_emulate_error() { return g_err.c_str(); }
