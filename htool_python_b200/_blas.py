@@ -8,6 +8,7 @@ from __future__ import annotations
 
 import ctypes
 import importlib.util
+import os
 from pathlib import Path
 
 _done = False
@@ -24,6 +25,8 @@ def preload() -> None:
     global _done
     if _done:
         return
+    # the bundled OpenBLAS is a pthreads build: nested inside the reference's OpenMP loops it must stay single-threaded
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
     d = openblas_dir()
     for pat in ("libquadmath-*.so*", "libgfortran-*.so*", "libopenblasp-*.so"):
         for lib in sorted(d.glob(pat)):

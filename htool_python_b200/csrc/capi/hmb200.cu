@@ -14,6 +14,10 @@ using namespace hmb200;
 
 static thread_local std::string g_last_error;
 
+// ABI layout pinned (mirrored by htool_python_b200/_lib.py and checked in tests/test_capi_symbols.py)
+static_assert(sizeof(hmb200_flat) == 96 && sizeof(hmb200_options) == 64 && sizeof(hmb200_info) == 120, "hmb200 ABI layout changed");
+static_assert(sizeof(PacketHeader) == 16 && sizeof(PieceDesc) == 16 && sizeof(StageEntry) == 32 && sizeof(ZCopy) == 8 && sizeof(WorkUnit) == 8 && sizeof(ReduceSeg) == 16, "packet layout changed");
+
 #define CUDA_CHECK(expr)                                                                                               \
     do {                                                                                                               \
         cudaError_t _e = (expr);                                                                                       \
