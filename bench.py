@@ -1,0 +1,339 @@
+#!/usr/bin/env python
+"""bench.py -- H-matvecs/sec of the N=1M Laplace 1/r H-matrix (BASELINE.json metric), 1..8 B200 vs the host CPU.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--n POINTS]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one H-matrix-vector product y = A x of the whole operator:
+  value  : device-resident (x, y replicated in cluster numbering in HBM; slab product + NCCL all-gather for N > 1),
+           timed with CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks;
+  e2e    : the same product through the reference-facing API (`B200HMatrix * x` / `B200DistributedOperator * x`) with
+           HOST numpy vectors in user numbering: pinned H2D, both permutations, product, D2H inside the timed region;
+  roofline: the dominant kernel's ALGORITHMIC bytes / its CUDA-event time vs MEASURED_PEAKS.json hbm_gbs;
+  cpu_baseline: the reference's own OpenMP product (oracle/_ref, compiled from the reference's sources) on the same
+           H-matrix object on this box's host cores.
+The H-matrix is assembled by the REFERENCE's builder (HMatrixTreeBuilder::build, OpenMP, native generator) on the host
+before the timed region; strong scaling: the N=1M operator is split into the reference's block-row slabs.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "H-matvecs/sec (N=1M Laplace 1/r, double, single RHS)"
+UNIT = "matvecs/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n", type=int, default=int(os.environ.get("HMB200_BENCH_N", 1_000_000)))
+    ap.add_argument("--eps", type=float, default=1e-3)
+    ap.add_argument("--eta", type=float, default=10.0)
+    ap.add_argument("--leaf", type=int, default=64)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--engine-opts", default="", help="k=v,k=v overrides of hmb200_options (tuning runs)")
+    return ap.parse_args()
+
+
+def sphere_points(n, seed=0):
+    """N points uniformly on the unit sphere surface (normalised Gaussian, seed 0) -- SURVEY.md 8(d) C2."""
+    g = np.random.default_rng(seed).standard_normal((3, n))
+    g /= np.linalg.norm(g, axis=0)
+    return np.asfortranarray(g)
+
+
+def host_threads(world):
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        cores = os.cpu_count() or 1
+    return max(1, cores // max(world, 1)), cores
+
+
+def assemble(args, world, rank, log):
+    """Cluster tree + this rank's block-row slab, assembled by the reference's own builders (bridge)."""
+    from htool_python_b200 import FlatHMatrix, bridge
+
+    t0 = time.time()
+    pts = sphere_points(args.n)
+    tree = bridge.create_cluster_tree(pts, 2, world, args.leaf)
+    t1 = time.time()
+    slab = rank if world > 1 else -1
+    H = bridge.build_hmatrix("laplace", tree, epsilon=args.eps, eta=args.eta, target_partition_number=slab,
+                             partition_number_for_symmetry=slab)
+    t2 = time.time()
+    flat = FlatHMatrix.from_htool(H)
+    log(f"rank {rank}: tree {t1 - t0:.1f}s, assembly {t2 - t1:.1f}s, leaves {flat.n_leaves}, W {flat.stored_coefficients:.4e}")
+    return tree, H, flat, dict(tree_s=t1 - t0, assembly_s=t2 - t1)
+
+
+class ClockSampler(threading.Thread):
+    """samples SM clock + throttle reasons of one GPU through NVML while the timed region runs"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.sm_max = index, False, [], set(), None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap", nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake", nv.nvmlClocksThrottleReasonSyncBoost: "sync_boost"}
+        while not self.stop_flag:
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def result(self):
+        self.stop_flag = True
+        if self.nv is None or not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": []}
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons)}
+
+
+def w_split(flat):
+    """algorithmic coefficients streamed by phase 1 (V factors) and phase 2 (U factors + dense leaves); DESIGN.md"""
+    r = np.maximum(flat.rank, 0).astype(np.float64)
+    lr = flat.rank >= 0
+    w1 = float(np.sum(r[lr] * flat.ncols[lr]))
+    w2 = float(np.sum(r[lr] * flat.nrows[lr]) + np.sum(flat.nrows[~lr].astype(np.float64) * flat.ncols[~lr]))
+    return w1, w2
+
+
+def run_b200(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    thr, cores = host_threads(world)
+    os.environ.setdefault("OMP_NUM_THREADS", str(thr))
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def log(msg):
+        print(f"[bench] {msg}", file=sys.stderr, flush=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    from htool_python_b200 import B200DistributedOperator, B200HMatrix
+
+    tree, H, flat, build_t = assemble(args, world, rank, log)
+    opts = {k: int(v) for k, v in (kv.split("=") for kv in args.engine_opts.split(",") if kv)}
+    t0 = time.time()
+    if world > 1:
+        op = B200DistributedOperator(flat, tree.partition, device=local_rank, **opts)
+        engine = op.engine
+    else:
+        op = B200HMatrix(flat, device=local_rank, **opts)
+        engine = op.engine
+    info = engine.info
+    log(f"rank {rank}: engine created in {time.time() - t0:.1f}s (pack {info['pack_seconds']:.1f}s upload {info['upload_seconds']:.1f}s) "
+        f"stream1 {info['stream1_bytes'] / 1e9:.2f} GB stream2 {info['stream2_bytes'] / 1e9:.2f} GB bins {info['n_bins']}")
+
+    n = args.n
+    rng = np.random.default_rng(1)
+    x_user = rng.random(n)  # U(0,1), seed 1
+    perm_s = flat.source_permutation
+    x_cluster = torch.from_numpy(np.ascontiguousarray(x_user[perm_s])).to(dev)
+    y_cluster = torch.zeros(n, dtype=torch.float64, device=dev)
+
+    if world > 1:
+        def step():
+            op.matvec_cluster_(x_cluster, y_cluster)
+    else:
+        def step():
+            engine.add_vector_product("N", 1.0, x_cluster, 0.0, y_cluster)
+
+    # ---- device-resident timed region ------------------------------------------------------------------------
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    engine.enable_timing(True)  # per-kernel CUDA events on the launching stream, collected after the region
+    launches0 = engine.launch_count
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    barrier()
+    clocks = sampler.result()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = engine.launch_count - launches0
+    kms = engine.kernel_ms_avg()
+    engine.enable_timing(False)
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+
+    # ---- end to end through the public API with host buffers ----------------------------------------------------
+    for _ in range(2):
+        y_user = op * x_user
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        y_user = op * x_user
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_step = float(t.item()) / args.steps
+
+    # ---- roofline of the dominant kernel (max over ranks of its time; this rank's bytes) ---------------------------
+    w1, w2 = w_split(flat)
+    es = 8
+    alg = {"phase1": es * (w1 + flat.n_cols), "phase2": es * (w2 + flat.n_rows)}
+    dom = "phase2" if kms["phase2"] >= kms["phase1"] else "phase1"
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6553.6))
+    achieved = alg[dom] / (kms[dom] * 1e-3) / 1e9 if kms[dom] > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": f"hmatrix_stream_kernel<double,{2 if dom == 'phase2' else 1}>", "achieved": round(achieved, 1),
+                "peak": peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback (B200_PROFILING.md)", "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": None, "algorithmic_bytes_per_launch": alg[dom],
+                "kernel_ms": {k: round(v, 4) for k, v in kms.items()},
+                "whole_product_GBps": round(flat.algorithmic_bytes(1) / (kms["total"] * 1e-3) / 1e9, 1) if kms["total"] > 0 else None}
+
+    # ---- CPU baseline + parity (rank 0, N=1 only) ---------------------------------------------------------------------
+    cpu = None
+    parity = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu, y_ref = cpu_reference_product(H, flat, x_user, thr, budget_s=15.0, log=log)
+        parity = float(np.linalg.norm(y_user - y_ref) / np.linalg.norm(y_ref))
+        log(f"parity vs reference CPU product: {parity:.3e}")
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": round(1e3 / ms_step, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": f"Laplace 1/(4 pi r) H-matrix, N={n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
+                                   f"leaf {args.leaf}, double, single-RHS matvec (BASELINE.json configs[1])",
+                       "partition": f"block-row slabs x{world}", "l2": "inputs larger than L2 (factor stream >> 126 MB, read once per step)",
+                       "stored_coefficients_rank0": flat.stored_coefficients, "leaves_rank0": flat.n_leaves,
+                       "assembly": "reference HMatrixTreeBuilder (OpenMP, native generator), outside the timed region", **build_t},
+            "clocks": clocks,
+            "e2e": {"value": round(1.0 / e2e_step, 3), "unit": UNIT, "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * n,
+                    "ms_per_step": round(e2e_step * 1e3, 4)},
+            "gpu_launches": int(launches),
+            "roofline": roofline,
+            "cpu_baseline": cpu,
+            "parity_rel_err_vs_reference": parity,
+        }
+        print(json.dumps(line), flush=True)
+    barrier()
+    op.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_reference_product(H, flat, x_user, threads, budget_s, log):
+    """times the REFERENCE's OpenMP product (add_hmatrix_vector_product(exec_compat::par), user numbering) on the host"""
+    import helpers_ref
+
+    ro = helpers_ref.ref_ops()
+    ro.omp_set_num_threads(threads)
+    fn = getattr(ro, "vector_product_user_addr_" + flat.dtype)
+    y = fn(H.address, x_user, True)  # warm-up
+    times = []
+    t_all = time.perf_counter()
+    while len(times) < 10 and (time.perf_counter() - t_all < budget_s or len(times) < 2):
+        t0 = time.perf_counter()
+        y = fn(H.address, x_user, True)
+        times.append(time.perf_counter() - t0)
+    best = min(times)
+    log(f"cpu reference product: {len(times)} runs, best {best * 1e3:.1f} ms, {threads} threads")
+    return {"value": round(1.0 / best, 4), "unit": UNIT, "cores": threads, "kind": "reference",
+            "sample": f"{len(times)} full matvecs of the same N={flat.n_cols} operator (best), reference OpenMP path "
+                      "add_hmatrix_vector_product(exec_compat::par) compiled from the reference sources (oracle/_ref)",
+            "ms_per_matvec": round(best * 1e3, 2)}, y
+
+
+def run_reference(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    thr, cores = host_threads(1)
+    os.environ.setdefault("OMP_NUM_THREADS", str(thr))
+
+    def log(msg):
+        print(f"[bench-ref] {msg}", file=sys.stderr, flush=True)
+
+    import helpers_ref
+
+    ro = helpers_ref.ref_ops()
+    ro.omp_set_num_threads(thr)
+    tree, H, flat, build_t = assemble(args, 1, 0, log)
+    x_user = np.random.default_rng(1).random(args.n)
+    fn = getattr(ro, "vector_product_user_addr_" + flat.dtype)
+    for _ in range(max(1, min(args.warmup, 3))):
+        fn(H.address, x_user, True)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        fn(H.address, x_user, True)
+    dt = (time.perf_counter() - t0) / args.steps
+    v = round(1.0 / dt, 4)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(dt * 1e3, 3), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"Laplace 1/(4 pi r) H-matrix, N={args.n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
+                                   f"leaf {args.leaf}, double, single-RHS matvec (BASELINE.json configs[1])", **build_t},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": thr, "kind": "reference",
+                             "sample": "each step = one full matvec, reference add_hmatrix_vector_product(exec_compat::par) from oracle/_ref"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse()
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

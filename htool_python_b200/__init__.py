@@ -6,7 +6,7 @@ products from hand-written sm_100a kernels (libhmb200.so, C ABI in include/hmb20
 """
 from .flat import FlatHMatrix  # noqa: F401
 
-__all__ = ["FlatHMatrix", "Engine", "B200HMatrix", "bridge"]
+__all__ = ["FlatHMatrix", "Engine", "B200HMatrix", "B200DistributedOperator", "bridge"]
 
 
 def __getattr__(name):
@@ -16,6 +16,9 @@ def __getattr__(name):
     if name == "B200HMatrix":
         from .hmatrix import B200HMatrix
         return B200HMatrix
+    if name == "B200DistributedOperator":
+        from .distributed import B200DistributedOperator
+        return B200DistributedOperator
     if name == "bridge":
         import importlib
         return importlib.import_module(".bridge", __name__)

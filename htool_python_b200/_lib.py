@@ -42,6 +42,7 @@ EXPORTS = {
     "hmb200_matmat_user_d": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int]),
     "hmb200_matmat_user_z": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int]),
     "hmb200_last_kernel_ms": (c_int, [c_void_p, POINTER(c_float * 4)]),
+    "hmb200_kernel_ms_avg": (c_int, [c_void_p, POINTER(c_float * 4), POINTER(c_int)]),
     "hmb200_enable_timing": (c_int, [c_void_p, c_int]),
     "hmb200_launch_count": (c_int64, [c_void_p]),
     "hmb200_last_error": (c_char_p, []),

@@ -66,7 +66,11 @@ struct hmb200_handle {
     size_t pinned_bytes = 0;
     uint32_t *counters = nullptr; // [2]
     int32_t *perm_t = nullptr, *perm_s = nullptr;
-    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    // per-kernel timing: a ring of CUDA-event quads recorded on the launching stream, collected lazily (no sync in the
+    // product path); kTimingSlots products are remembered
+    static constexpr int kTimingSlots = 256;
+    std::vector<cudaEvent_t> ev; // 4 per slot
+    int64_t timed_products = 0;  // products recorded since timing was enabled
     bool timing = false;
     float last_ms[4] = {0, 0, 0, 0};
     int64_t launches = 0;
@@ -225,7 +229,6 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
         CUDA_CHECK(cudaMalloc(&h->xz, (size_t)(h->xz_elems + 4) * es));
         CUDA_CHECK(cudaMemsetAsync(h->xz, 0, (size_t)(h->xz_elems + 4) * es, h->stream));
         CUDA_CHECK(cudaMalloc(&h->counters, 64));
-        for (auto &ev : h->ev) CUDA_CHECK(cudaEventCreate(&ev));
         size_t s1 = stream_smem_bytes(1, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps);
         size_t s2 = stream_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps);
         if (es == 8) set_kernel_attrs<double>(s1, s2); else set_kernel_attrs<double2>(s1, s2);
@@ -285,7 +288,16 @@ void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const doub
     p.beta_re  = beta[0];  p.beta_im  = h->es == 16 ? beta[1] : 0.0;
     p.stage_bytes = o.stage_bytes; p.z_bytes = o.stage_z_bytes; p.n_stages = o.n_stages; p.consumer_warps = o.consumer_warps;
     CUDA_CHECK(cudaMemsetAsync(h->counters, 0, 64, h->stream));
-    if (h->timing) CUDA_CHECK(cudaEventRecord(h->ev[0], h->stream));
+    cudaEvent_t *ev = nullptr;
+    if (h->timing) {
+        if (h->ev.empty()) {
+            h->ev.resize(4 * hmb200_handle::kTimingSlots, nullptr);
+            for (auto &e : h->ev) CUDA_CHECK(cudaEventCreate(&e));
+        }
+        ev = h->ev.data() + 4 * (h->timed_products % hmb200_handle::kTimingSlots);
+        h->timed_products++;
+        CUDA_CHECK(cudaEventRecord(ev[0], h->stream));
+    }
     if (po.n_units[0] > 0) {
         p.stream = po.stream[0]; p.stages = po.stages[0]; p.zcopies = po.zcopies[0]; p.units = po.units[0];
         p.n_units = po.n_units[0]; p.counter = h->counters;
@@ -293,13 +305,13 @@ void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const doub
         hmatrix_stream_kernel<T, 1><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[0]), threads, smem, h->stream>>>(p);
         h->launches++;
     }
-    if (h->timing) CUDA_CHECK(cudaEventRecord(h->ev[1], h->stream));
+    if (ev) CUDA_CHECK(cudaEventRecord(ev[1], h->stream));
     if (po.n_reduce > 0) {
         unsigned blocks = (po.n_reduce + 7) / 8;
         reduce_partials_kernel<T><<<blocks, 256, 0, h->stream>>>(po.reduce, po.n_reduce, (T *)h->xz);
         h->launches++;
     }
-    if (h->timing) CUDA_CHECK(cudaEventRecord(h->ev[2], h->stream));
+    if (ev) CUDA_CHECK(cudaEventRecord(ev[2], h->stream));
     if (po.n_units[1] > 0) {
         p.stream = po.stream[1]; p.stages = po.stages[1]; p.zcopies = po.zcopies[1]; p.units = po.units[1];
         p.n_units = po.n_units[1]; p.counter = h->counters + 1;
@@ -307,15 +319,28 @@ void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const doub
         hmatrix_stream_kernel<T, 2><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]), threads, smem, h->stream>>>(p);
         h->launches++;
     }
-    if (h->timing) CUDA_CHECK(cudaEventRecord(h->ev[3], h->stream));
+    if (ev) CUDA_CHECK(cudaEventRecord(ev[3], h->stream));
     CUDA_CHECK(cudaGetLastError());
 }
 
-void collect_timing(hmb200_handle *h) {
-    if (!h->timing) return;
-    CUDA_CHECK(cudaEventSynchronize(h->ev[3]));
-    for (int i = 0; i < 3; i++) CUDA_CHECK(cudaEventElapsedTime(&h->last_ms[i], h->ev[i], h->ev[i + 1]));
-    CUDA_CHECK(cudaEventElapsedTime(&h->last_ms[3], h->ev[0], h->ev[3]));
+// averages the per-kernel times of the last min(timed_products, kTimingSlots) products into ms[4]; returns the count
+int collect_timing(hmb200_handle *h, float ms[4], bool last_only) {
+    for (int i = 0; i < 4; i++) ms[i] = 0;
+    const int64_t have = std::min<int64_t>(h->timed_products, hmb200_handle::kTimingSlots);
+    if (have == 0 || h->ev.empty()) return 0;
+    const int64_t first = last_only ? h->timed_products - 1 : h->timed_products - have;
+    double acc[4] = {0, 0, 0, 0};
+    int n = 0;
+    for (int64_t k = first; k < h->timed_products; k++, n++) {
+        cudaEvent_t *ev = h->ev.data() + 4 * (k % hmb200_handle::kTimingSlots);
+        CUDA_CHECK(cudaEventSynchronize(ev[3]));
+        float t;
+        for (int i = 0; i < 3; i++) { CUDA_CHECK(cudaEventElapsedTime(&t, ev[i], ev[i + 1])); acc[i] += t; }
+        CUDA_CHECK(cudaEventElapsedTime(&t, ev[0], ev[3]));
+        acc[3] += t;
+    }
+    for (int i = 0; i < 4; i++) ms[i] = (float)(acc[i] / n);
+    return n;
 }
 
 template <typename T>
@@ -327,7 +352,6 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
     if (mem == HMB200_DEVICE) {
         CUDA_CHECK(cudaMemcpyAsync(h->xz, in, in_b, cudaMemcpyDeviceToDevice, h->stream));
         run_product<T>(h, po, alpha, beta, out, nullptr);
-        if (h->timing) collect_timing(h);
     } else {
         ensure_pinned(h, in_b + out_b + 64);
         ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out, h->es);
@@ -342,7 +366,6 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
         CUDA_CHECK(cudaMemcpyAsync(pout, h->ybuf, out_b, cudaMemcpyDeviceToHost, h->stream));
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
         std::memcpy(out, pout, out_b);
-        collect_timing(h);
     }
     return 0;
 }
@@ -427,9 +450,6 @@ int matvec_user(hmb200_handle *h, const void *x, void *y, int mem, int mu) {
         CUDA_CHECK(cudaMemcpyAsync(pout, dy, out_b, cudaMemcpyDeviceToHost, h->stream));
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
         std::memcpy(y, pout, out_b);
-        collect_timing(h);
-    } else if (h->timing) {
-        collect_timing(h);
     }
     return 0;
 }
@@ -482,6 +502,7 @@ void hmb200_destroy(hmb200_handle *h) {
     if (h->pinned) cudaFreeHost(h->pinned);
     for (auto &ev : h->ev)
         if (ev) cudaEventDestroy(ev);
+    h->ev.clear();
     delete h;
 }
 
@@ -579,12 +600,19 @@ int hmb200_matmat_user_z(hmb200_handle *h, const double *X, double *Y, int mu, i
 }
 
 int hmb200_last_kernel_ms(hmb200_handle *h, float ms[4]) {
-    if (!h || !ms) { g_last_error = "null argument"; return 1; }
-    for (int i = 0; i < 4; i++) ms[i] = h->last_ms[i];
-    return 0;
+    return guarded([&] { if (!h || !ms) throw std::runtime_error("null argument"); collect_timing(h, ms, true); return 0; });
+}
+int hmb200_kernel_ms_avg(hmb200_handle *h, float ms[4], int *n_products) {
+    return guarded([&] {
+        if (!h || !ms) throw std::runtime_error("null argument");
+        int n = collect_timing(h, ms, false);
+        if (n_products) *n_products = n;
+        return 0;
+    });
 }
 int hmb200_enable_timing(hmb200_handle *h, int on) {
     if (!h) { g_last_error = "null handle"; return 1; }
+    if (on && !h->timing) h->timed_products = 0; // (re)start the averaging window
     h->timing = on != 0;
     return 0;
 }

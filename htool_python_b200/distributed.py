@@ -1,0 +1,180 @@
+"""`B200DistributedOperator`: the block-row product of the reference's `DistributedOperator`, one process per GPU.
+
+Mirrors (paths under /root/reference/lib/htool/include/htool/distributed_operator):
+  * the partition of the target cluster tree into contiguous row slabs, one per rank
+    (implementations/partition_from_cluster.hpp:11-42, utility.hpp:56: rank p holds cluster_on_partition(p) x source root);
+  * `__mul__` / `__matmul__` = add_distributed_operator_{vector,matrix}_product_global_to_global
+    (linalg/add_distributed_operator_vector_product_global_to_global.hpp:18-118,
+     linalg/add_distributed_operator_matrix_product_global_to_global.hpp:138-280):
+        x_user --global_to_root_cluster--> x_cluster (replicated)
+        slab_p = H_p x_cluster                       (this rank's engine, hand-written sm_100a kernels)
+        all-gather of the slabs                      (reference: MPI_Allgatherv :76; here NCCL over NVLink)
+        y_cluster --root_cluster_to_global--> y_user
+  * the solver entry (linalg/add_distributed_operator_vector_product_local_to_local.hpp:19-89): the gathered,
+    replicated cluster-numbered vector is exactly the input of the next product, so `matvec_cluster_` keeps it on
+    the device and GMRES never leaves the GPU.
+
+The collective runs on `torch.distributed` (backend "nccl" on GPUs; "gloo" works for the CPU tests of the host logic with
+a stand-in slab product).  Slabs are disjoint and contiguous in cluster numbering, so the all-gather is in place.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib
+
+
+def partition_displacements(partition: Sequence[Tuple[int, int]]):
+    """(offsets, sizes) of the rank slabs; checks they tile [0, n) contiguously (partition_from_cluster.hpp:22-25)."""
+    offs = [int(o) for o, _ in partition]
+    sizes = [int(s) for _, s in partition]
+    cur = 0
+    for o, s in zip(offs, sizes):
+        if o != cur or s < 0:
+            raise ValueError("partition slabs must be contiguous and ordered by rank")
+        cur += s
+    return offs, sizes
+
+
+def allgather_slabs_(buf, offs: List[int], sizes: List[int], mu: int, group=None):
+    """In-place all-gather of row slabs of the replicated row-major (n x mu) tensor `buf`: afterwards every rank holds
+    every slab (MPI_Allgatherv of add_distributed_operator_vector_product_global_to_global.hpp:76)."""
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    if world == 1:
+        return buf
+    rank = dist.get_rank(group)
+    flat = buf.view(-1)
+    if len(set(sizes)) == 1 and flat.numel() == world * sizes[0] * mu:
+        mine = flat[offs[rank] * mu:(offs[rank] + sizes[rank]) * mu]
+        dist.all_gather_into_tensor(flat, mine, group=group)  # in place: slab p already sits at p*count
+    else:  # unequal slabs: one broadcast per rank (P <= 8)
+        for p in range(world):
+            if sizes[p]:
+                dist.broadcast(flat[offs[p] * mu:(offs[p] + sizes[p]) * mu], src=dist.get_global_rank(group, p) if group is not None else p, group=group)
+    return buf
+
+
+class B200DistributedOperator:
+    """Drop-in for the product surface of `Htool.DistributedOperator` (`shape`, `*`, `@`;
+    src/htool/distributed_operator/distributed_operator.hpp:16-65) backed by one `Engine` per rank.
+
+    slab_flat : FlatHMatrix of THIS rank's row slab (n_rows = local size, n_cols = global source size), as assembled by
+                the reference with target_partition_number = rank
+    partition : [(offset, size)] of every rank's slab in target cluster numbering
+    """
+
+    def __init__(self, slab_flat, partition, group=None, device: Optional[int] = None, **options):
+        import torch
+        import torch.distributed as dist
+
+        from .engine import Engine
+
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.offs, self.sizes = partition_displacements(partition)
+        if len(self.offs) != self.world:
+            raise ValueError(f"partition has {len(self.offs)} slabs but the process group has {self.world} ranks")
+        if slab_flat.n_rows != self.sizes[self.rank] or slab_flat.target_offset != self.offs[self.rank]:
+            raise ValueError("slab_flat is not this rank's slab of the partition")
+        self.n_target = sum(self.sizes)
+        self.n_source = slab_flat.n_cols
+        self.engine = Engine(slab_flat, device=device, **options)
+        self.device = torch.device("cuda", self.engine.device)
+        self.is_complex = self.engine.is_complex
+        self.np_dtype = self.engine.np_dtype
+        self.torch_dtype = torch.complex128 if self.is_complex else torch.float64
+        self.es = 16 if self.is_complex else 8
+        if slab_flat.target_permutation is None or len(slab_flat.target_permutation) != self.n_target:
+            raise ValueError("slab_flat must carry the full target / source permutations")
+        self.perm_t = torch.from_numpy(np.ascontiguousarray(slab_flat.target_permutation, np.int32)).to(self.device)
+        self.perm_s = torch.from_numpy(np.ascontiguousarray(slab_flat.source_permutation, np.int32)).to(self.device)
+        self._x = {}  # mu -> (x_cluster, y_cluster) replicated device buffers
+        self._pin = {}
+
+    @property
+    def shape(self):
+        return (self.n_target, self.n_source)
+
+    # ---- device-resident products in cluster numbering -------------------------------------------------------
+    def matvec_cluster_(self, x_cluster, y_cluster):
+        """y_cluster (replicated, length n_target) = A x_cluster; both CUDA tensors; slab product + all-gather."""
+        o, s = self.offs[self.rank], self.sizes[self.rank]
+        self.engine.add_vector_product("N", 1.0, x_cluster, 0.0, y_cluster[o:o + s])
+        return allgather_slabs_(y_cluster, self.offs, self.sizes, 1, self.group)
+
+    def matmat_cluster_(self, X_cluster, Y_cluster, mu: int):
+        """row-major (n x mu) blocks (add_distributed_operator_matrix_product_row_major_global_to_global.hpp:18-84)."""
+        o, s = self.offs[self.rank], self.sizes[self.rank]
+        self.engine.add_matrix_product_row_major("N", 1.0, X_cluster, 0.0, Y_cluster.view(-1)[o * mu:(o + s) * mu], mu)
+        return allgather_slabs_(Y_cluster, self.offs, self.sizes, mu, self.group)
+
+    # ---- user-numbering products on host arrays (what the reference's Python API does) ------------------------
+    def _permute(self, gather: bool, perm, n, src, dst, mu):
+        import torch
+
+        fn = _lib.lib().hmb200_permute_gather if gather else _lib.lib().hmb200_permute_scatter
+        _lib.check(fn(perm.data_ptr(), 0, n, src.data_ptr(), dst.data_ptr(), self.es, mu, _lib.DEVICE,
+                      torch.cuda.current_stream(self.device).cuda_stream))
+
+    def _buffers(self, mu):
+        import torch
+
+        if mu not in self._x:
+            mk = lambda n: torch.empty(n * mu, dtype=self.torch_dtype, device=self.device)  # noqa: E731
+            self._x[mu] = (mk(self.n_source), mk(self.n_source), mk(self.n_target), mk(self.n_target))
+            self._pin[mu] = (torch.empty(self.n_source * mu, dtype=self.torch_dtype).pin_memory(),
+                             torch.empty(self.n_target * mu, dtype=self.torch_dtype).pin_memory())
+        return self._x[mu], self._pin[mu]
+
+    def __mul__(self, x):
+        import torch
+
+        x = np.asarray(x)
+        if x.ndim != 1:
+            raise RuntimeError("Wrong dimension for HMatrix-vector product")  # distributed_operator.hpp:25-27
+        if x.shape[0] != self.n_source:
+            raise RuntimeError("Wrong size for HMatrix-vector product")
+        (xu, xc, yc, yu), (pin_x, pin_y) = self._buffers(1)
+        with torch.cuda.device(self.device):
+            pin_x.numpy()[:] = x.astype(self.np_dtype, copy=False)
+            xu.copy_(pin_x, non_blocking=True)
+            self._permute(True, self.perm_s, self.n_source, xu, xc, 1)     # global_to_root_cluster (:108)
+            self.matvec_cluster_(xc, yc)
+            self._permute(False, self.perm_t, self.n_target, yc, yu, 1)    # root_cluster_to_global (:117)
+            pin_y.copy_(yu, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+        return pin_y.numpy().copy()
+
+    def __matmul__(self, X):
+        """X: (n_source, mu) Fortran-ordered like the reference (distributed_operator.hpp:39-65); result F-ordered."""
+        import torch
+
+        X = np.asarray(X)
+        if X.ndim != 2:
+            raise RuntimeError("Wrong dimension for HMatrix-matrix product")
+        if X.shape[0] != self.n_source:
+            raise RuntimeError("Wrong size for HMatrix-matrix product")
+        mu = X.shape[1]
+        (xu, xc, yc, yu), (pin_x, pin_y) = self._buffers(mu)
+        with torch.cuda.device(self.device):
+            # host side of the reference does per-column permutation + transpose to row-major (:176-187); here the
+            # column-major block is permuted on the device and transposed by a strided view copy
+            pin_x.numpy()[:] = np.asfortranarray(X, dtype=self.np_dtype).reshape(-1, order="F")
+            xu.copy_(pin_x, non_blocking=True)
+            self._permute(True, self.perm_s, self.n_source, xu, xc, mu)    # column-major, per column
+            xr = xc.view(mu, self.n_source).t().contiguous()               # -> row-major n x mu
+            yr = yu.view(self.n_target, mu)
+            self.matmat_cluster_(xr.view(-1), yr, mu)
+            yc.view(mu, self.n_target).copy_(yr.t())                        # back to column-major
+            self._permute(False, self.perm_t, self.n_target, yc, yu, mu)
+            pin_y.copy_(yu, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+        return np.array(pin_y.numpy().reshape((self.n_target, mu), order="F"), order="F")
+
+    def close(self):
+        self.engine.close()

@@ -54,7 +54,9 @@ class Engine:
             raise RuntimeError("hmb200_create failed: " + _lib.last_error())
         self._h = ctypes.c_void_p(h)
         self._has_perms = False
-        if flat.target_permutation is not None and len(flat.target_permutation):
+        # user-numbering products need the root block of both trees (a row slab's slots map to arbitrary user indices)
+        if (flat.target_permutation is not None and len(flat.target_permutation) == flat.n_rows and flat.target_offset == 0
+                and flat.source_permutation is not None and len(flat.source_permutation) == flat.n_cols and flat.source_offset == 0):
             tp, sp = flat.local_target_permutation(), flat.local_source_permutation()
             _lib.check(lib.hmb200_set_permutations(self._h, tp.ctypes.data, sp.ctypes.data))
             self._has_perms = True
@@ -84,6 +86,12 @@ class Engine:
         ms = (ctypes.c_float * 4)()
         _lib.check(_lib.lib().hmb200_last_kernel_ms(self._h, ctypes.byref(ms)))
         return dict(phase1=ms[0], reduce=ms[1], phase2=ms[2], total=ms[3])
+
+    def kernel_ms_avg(self):
+        """per-kernel CUDA-event times averaged over the products issued since enable_timing(True)"""
+        ms, n = (ctypes.c_float * 4)(), ctypes.c_int(0)
+        _lib.check(_lib.lib().hmb200_kernel_ms_avg(self._h, ctypes.byref(ms), ctypes.byref(n)))
+        return dict(phase1=ms[0], reduce=ms[1], phase2=ms[2], total=ms[3], products=n.value)
 
     @property
     def launch_count(self) -> int:

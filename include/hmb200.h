@@ -129,6 +129,9 @@ int hmb200_matmat_user_z(hmb200_handle *h, const double *X, double *Y, int mu, i
 /* timing of the kernels of the last product on the handle's stream (CUDA events), in milliseconds:
  * ms[0] phase 1 (t = V x), ms[1] partial reduce, ms[2] phase 2 (y += U t, y += D x), ms[3] whole product */
 int hmb200_last_kernel_ms(hmb200_handle *h, float ms[4]);
+/* the same, averaged over the (up to 256) products issued since hmb200_enable_timing(h, 1); events are recorded on the
+ * launching stream without synchronising, and collected here */
+int hmb200_kernel_ms_avg(hmb200_handle *h, float ms[4], int *n_products);
 int hmb200_enable_timing(hmb200_handle *h, int on);
 /* number of kernel launches issued by this handle since creation */
 int64_t hmb200_launch_count(const hmb200_handle *h);
