@@ -73,12 +73,21 @@ def assemble(args, world, rank, log):
     tree = bridge.create_cluster_tree(pts, 2, world, args.leaf)
     t1 = time.time()
     slab = rank if world > 1 else -1
+    # keep every admissible block below 46340 x 46340: the reference's ACA stop test `q*(n1+n2) > n1*n2` is int arithmetic
+    # (lib/htool/include/htool/hmatrix/lrmat/sympartialACA.hpp:102); above that it overflows and the block is built DENSE
+    depth = 0
+    while args.n / 2 ** depth > 46340:
+        depth += 1
+    depth += 1 if depth else 0  # the builder's depth test is off by one against size = n / 2^depth (measured)
     H = bridge.build_hmatrix("laplace", tree, epsilon=args.eps, eta=args.eta, target_partition_number=slab,
-                             partition_number_for_symmetry=slab)
+                             partition_number_for_symmetry=slab, minimal_target_depth=depth, minimal_source_depth=depth)
     t2 = time.time()
     flat = FlatHMatrix.from_htool(H)
+    big = (flat.rank < 0) & (flat.nrows.astype(np.int64) * flat.ncols > 1 << 22)
+    if big.any():
+        raise RuntimeError(f"the reference built {int(big.sum())} dense blocks above 4M coefficients (ACA int overflow?)")
     log(f"rank {rank}: tree {t1 - t0:.1f}s, assembly {t2 - t1:.1f}s, leaves {flat.n_leaves}, W {flat.stored_coefficients:.4e}")
-    return tree, H, flat, dict(tree_s=t1 - t0, assembly_s=t2 - t1)
+    return tree, H, flat, dict(tree_s=round(t1 - t0, 2), assembly_s=round(t2 - t1, 2), minimal_block_depth=depth)
 
 
 class ClockSampler(threading.Thread):

@@ -31,11 +31,13 @@ def create_cluster_tree(points, number_of_children=2, size_of_partition=1, maxim
 
 
 def build_hmatrix(kernel, target_tree, source_tree=None, epsilon=1e-3, eta=10.0, symmetry="N", UPLO="N",
-                  target_partition_number=-1, partition_number_for_symmetry=-1, wavenumber=0.0, parallel=True):
+                  target_partition_number=-1, partition_number_for_symmetry=-1, wavenumber=0.0, parallel=True,
+                  minimal_target_depth=0, minimal_source_depth=0):
     """Assemble with the reference's HMatrixTreeBuilder::build and a native C++ generator for `kernel`."""
     br = module()
     source_tree = target_tree if source_tree is None else source_tree
     kid = br.KERNELS[kernel]
     fn = br.build_complex_hmatrix if kernel in COMPLEX_KERNELS else br.build_hmatrix
     return fn(kid, float(wavenumber), target_tree, source_tree, float(epsilon), float(eta), symmetry, UPLO,
-              int(target_partition_number), int(partition_number_for_symmetry), bool(parallel))
+              int(target_partition_number), int(partition_number_for_symmetry), bool(parallel),
+              int(minimal_target_depth), int(minimal_source_depth))

@@ -144,12 +144,17 @@ static std::shared_ptr<NativeClusterTree> make_cluster_tree(py::array_t<double, 
 }
 
 template <typename T>
-static std::shared_ptr<NativeHMatrix<T>> build_hmatrix(int kernel_id, double wavenumber, std::shared_ptr<NativeClusterTree> target, std::shared_ptr<NativeClusterTree> source, double epsilon, double eta, char symmetry, char UPLO, int target_partition_number, int partition_number_for_symmetry, bool parallel) {
+static std::shared_ptr<NativeHMatrix<T>> build_hmatrix(int kernel_id, double wavenumber, std::shared_ptr<NativeClusterTree> target, std::shared_ptr<NativeClusterTree> source, double epsilon, double eta, char symmetry, char UPLO, int target_partition_number, int partition_number_for_symmetry, bool parallel, int minimal_target_depth, int minimal_source_depth) {
     auto h       = std::make_shared<NativeHMatrix<T>>();
     h->target    = target;
     h->source    = source;
     h->generator = std::make_shared<NativeKernelGenerator<T>>(kernel_id, target->dim, wavenumber, target->points, source->points);
     HMatrixTreeBuilder<T, double> tree_builder(epsilon, eta, symmetry, UPLO);
+    // the reference's own setters (src/htool/hmatrix/hmatrix_tree_builder.hpp binds them too): admissible blocks are only
+    // accepted below these depths.  Needed at N >= ~90k per side: sympartialACA's `q*(n1+n2) > n1*n2` is `int` arithmetic
+    // (hmatrix/lrmat/sympartialACA.hpp:102) and overflows for blocks above 46340 x 46340, which turns them into DENSE blocks.
+    tree_builder.set_minimal_target_depth(minimal_target_depth);
+    tree_builder.set_minimal_source_depth(minimal_source_depth);
     {
         py::gil_scoped_release release;
         if (parallel)
@@ -307,8 +312,8 @@ PYBIND11_MODULE(_htool_bridge, m) {
     declare_native<zdouble>(m, "NativeComplexHMatrix");
 
     m.def("create_cluster_tree", &make_cluster_tree, py::arg("coordinates"), py::arg("number_of_children") = 2, py::arg("size_of_partition") = 1, py::arg("maximal_leaf_size") = 64);
-    m.def("build_hmatrix", &build_hmatrix<double>, py::arg("kernel_id"), py::arg("wavenumber"), py::arg("target"), py::arg("source"), py::arg("epsilon"), py::arg("eta"), py::arg("symmetry") = 'N', py::arg("UPLO") = 'N', py::arg("target_partition_number") = -1, py::arg("partition_number_for_symmetry") = -1, py::arg("parallel") = true);
-    m.def("build_complex_hmatrix", &build_hmatrix<zdouble>, py::arg("kernel_id"), py::arg("wavenumber"), py::arg("target"), py::arg("source"), py::arg("epsilon"), py::arg("eta"), py::arg("symmetry") = 'N', py::arg("UPLO") = 'N', py::arg("target_partition_number") = -1, py::arg("partition_number_for_symmetry") = -1, py::arg("parallel") = true);
+    m.def("build_hmatrix", &build_hmatrix<double>, py::arg("kernel_id"), py::arg("wavenumber"), py::arg("target"), py::arg("source"), py::arg("epsilon"), py::arg("eta"), py::arg("symmetry") = 'N', py::arg("UPLO") = 'N', py::arg("target_partition_number") = -1, py::arg("partition_number_for_symmetry") = -1, py::arg("parallel") = true, py::arg("minimal_target_depth") = 0, py::arg("minimal_source_depth") = 0);
+    m.def("build_complex_hmatrix", &build_hmatrix<zdouble>, py::arg("kernel_id"), py::arg("wavenumber"), py::arg("target"), py::arg("source"), py::arg("epsilon"), py::arg("eta"), py::arg("symmetry") = 'N', py::arg("UPLO") = 'N', py::arg("target_partition_number") = -1, py::arg("partition_number_for_symmetry") = -1, py::arg("parallel") = true, py::arg("minimal_target_depth") = 0, py::arg("minimal_source_depth") = 0);
 
     // the reference's own Python objects (only resolvable once `import Htool` has registered the types)
     m.def("flat_view", [](const HMatrix<double, double> &H) { return flat_view(H); });
