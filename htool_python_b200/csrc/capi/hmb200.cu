@@ -36,6 +36,7 @@ struct PackedOp {
     ZCopy *zcopies[2]     = {nullptr, nullptr};
     WorkUnit *units[2]    = {nullptr, nullptr};
     uint32_t n_units[2]   = {0, 0};
+    uint32_t n_zcopies[2] = {0, 0};
     ReduceSeg *reduce     = nullptr;
     uint32_t n_reduce     = 0;
     uint64_t xz_elems     = 0;
@@ -157,6 +158,7 @@ void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) 
         po.zcopies[ph]      = upload_vec(pp.zcopies, h->stream);
         po.units[ph]        = upload_vec(pp.units, h->stream);
         po.n_units[ph]      = (uint32_t)pp.units.size();
+        po.n_zcopies[ph]    = (uint32_t)pp.zcopies.size();
         po.stream_bytes[ph] = pp.stream_bytes;
         po.n_stages[ph]     = pp.stages.size();
         po.table_bytes += pp.stages.size() * sizeof(StageEntry) + pp.zcopies.size() * sizeof(ZCopy) + pp.units.size() * sizeof(WorkUnit);
@@ -300,7 +302,7 @@ void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const doub
     }
     if (po.n_units[0] > 0) {
         p.stream = po.stream[0]; p.stages = po.stages[0]; p.zcopies = po.zcopies[0]; p.units = po.units[0];
-        p.n_units = po.n_units[0]; p.counter = h->counters;
+        p.n_units = po.n_units[0]; p.n_zcopies = po.n_zcopies[0]; p.counter = h->counters;
         size_t smem = stream_smem_bytes(1, h->es, o.stage_bytes, o.stage_z_bytes, o.n_stages, o.consumer_warps);
         hmatrix_stream_kernel<T, 1><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[0]), threads, smem, h->stream>>>(p);
         h->launches++;
@@ -314,7 +316,7 @@ void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const doub
     if (ev) CUDA_CHECK(cudaEventRecord(ev[2], h->stream));
     if (po.n_units[1] > 0) {
         p.stream = po.stream[1]; p.stages = po.stages[1]; p.zcopies = po.zcopies[1]; p.units = po.units[1];
-        p.n_units = po.n_units[1]; p.counter = h->counters + 1;
+        p.n_units = po.n_units[1]; p.n_zcopies = po.n_zcopies[1]; p.counter = h->counters + 1;
         size_t smem = stream_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_bytes, o.n_stages, o.consumer_warps);
         hmatrix_stream_kernel<T, 2><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]), threads, smem, h->stream>>>(p);
         h->launches++;

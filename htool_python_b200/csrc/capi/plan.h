@@ -32,8 +32,8 @@ struct PieceDesc { // 16 B
     uint16_t z_off;    // element offset inside the stage z-area of the operand slice
     uint16_t nc;       // phase 2: columns; phase 1: nq (columns of the V tile)
     uint8_t nr;        // phase 2: rows (<= 64); phase 1: lr (<= 32)
-    uint8_t ro;        // phase 2: first row inside the bin
-    uint16_t pad;
+    uint8_t ro;        // phase 2: first row inside the bin; phase 1: G = 32 / lr column groups
+    uint16_t pad;      // phase 1: ceil(32768 / lr), so that lane / lr == (lane * pad) >> 15
 };
 
 struct StageEntry { // 32 B, read by the producer warp

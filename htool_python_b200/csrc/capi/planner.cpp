@@ -89,6 +89,13 @@ static void make_vleaves(const hmb200_flat &f, char op, Plan &plan) {
             push(l, op == 'N', op == 'N' && sym == 'H');
     }
     plan.stored_coefficients = W;
+    // order the views by output range: all views with the same target cluster become neighbours, so do their t slots
+    // (assigned in this order) and the phase-2 pieces of a bin -- one operand copy then serves many tiles of a stage
+    std::stable_sort(plan.vleaves.begin(), plan.vleaves.end(), [](const VLeaf &a, const VLeaf &b) {
+        if (a.row_off != b.row_off) return a.row_off < b.row_off;
+        if (a.m != b.m) return a.m > b.m;
+        return a.col_off < b.col_off;
+    });
 }
 
 // target bins: ranges of <= bin_rows output rows, aligned with the leaves' cluster boundaries where possible
@@ -158,14 +165,41 @@ struct StageBuilder {
         first_piece = piece_index; n_pieces = 0; data_bytes = 0; z_bytes = 0; z_first = (uint32_t)ph.zcopies.size();
         tile_bytes.clear();
     }
-    // adds piece `piece_index` (must be consecutive); z source span given in xz elements
+    // adds the next piece; its operand is the xz element span [z_src, z_src + z_cnt).  Operand copies are the expensive
+    // part of a stage for the TMA unit (each small cp.async.bulk has a fixed cost), so a span is (1) served from a copy
+    // this stage already makes if it lies inside one, (2) appended to the last copy if it overlaps / touches its end,
+    // and only otherwise (3) becomes a new copy.  The planner orders pieces so that (1) and (2) are the common case.
     void add(uint32_t tile, uint32_t z_src, uint32_t z_cnt) {
         uint32_t src_al, zb, lead;
         aligned_span(es, z_src, z_cnt, src_al, zb, lead);
-        ZCopy zc; zc.src_elem = src_al; zc.bytes = (uint16_t)zb; zc.dst_off = (uint16_t)z_bytes;
-        ph.zcopies.push_back(zc);
-        ph.piece_zoff.push_back((uint16_t)(z_bytes / es + lead));
-        z_bytes += zb;
+        const uint32_t end_al = src_al + zb / es; // element index one past the aligned span
+        uint32_t zoff = UINT32_MAX;
+        for (size_t c = ph.zcopies.size(); c-- > z_first;) { // (1) contained in an earlier copy of this stage
+            const ZCopy &zc = ph.zcopies[c];
+            if (src_al >= zc.src_elem && end_al <= zc.src_elem + zc.bytes / (uint32_t)es) {
+                zoff = zc.dst_off / es + (z_src - zc.src_elem);
+                break;
+            }
+        }
+        if (zoff == UINT32_MAX && ph.zcopies.size() > z_first) { // (2) extend the last copy
+            ZCopy &zc = ph.zcopies.back();
+            const uint32_t last_end = zc.src_elem + zc.bytes / (uint32_t)es;
+            if (src_al >= zc.src_elem && src_al <= last_end) {
+                const uint32_t grow = (end_al - last_end) * es;
+                if ((uint32_t)zc.bytes + grow <= 65520u) {
+                    zoff = zc.dst_off / es + (z_src - zc.src_elem);
+                    zc.bytes = (uint16_t)(zc.bytes + grow);
+                    z_bytes += grow;
+                }
+            }
+        }
+        if (zoff == UINT32_MAX) { // (3) new copy
+            ZCopy zc; zc.src_elem = src_al; zc.bytes = (uint16_t)zb; zc.dst_off = (uint16_t)z_bytes;
+            ph.zcopies.push_back(zc);
+            zoff = z_bytes / es + lead;
+            z_bytes += zb;
+        }
+        ph.piece_zoff.push_back((uint16_t)zoff);
         tile_bytes.push_back(align_up(tile, 16));
         data_bytes += align_up(tile, 16);
         n_pieces++;
@@ -179,7 +213,7 @@ struct StageBuilder {
         se.gmem_off = ph.stream_bytes;
         se.bytes    = hdr + data_bytes;
         se.z_first  = z_first;
-        se.n_z      = n_pieces;
+        se.n_z      = (uint32_t)ph.zcopies.size() - z_first;
         se.z_bytes  = z_bytes;
         ph.stages.push_back(se);
         uint32_t off = hdr;
@@ -217,9 +251,20 @@ void build_plan(const hmb200_flat &f, int es, char op, const Options &opt, Plan 
 
     // ---- phase 1 pieces: V-role tiles --------------------------------------------------------------------
     const uint32_t zmax_elems = (uint32_t)(opt.stage_z_bytes / es) - 2;
-    for (size_t vi = 0; vi < plan.vleaves.size(); vi++) {
+    // phase-1 tiles are visited by input range (source cluster): V tiles of different leaves that multiply the same slice
+    // of x land in the same stage and share one operand copy
+    std::vector<uint32_t> order1;
+    order1.reserve(plan.vleaves.size());
+    for (size_t vi = 0; vi < plan.vleaves.size(); vi++)
+        if (plan.vleaves[vi].r > 0) order1.push_back((uint32_t)vi);
+    std::stable_sort(order1.begin(), order1.end(), [&](uint32_t a, uint32_t b) {
+        const VLeaf &x = plan.vleaves[a], &y = plan.vleaves[b];
+        if (x.col_off != y.col_off) return x.col_off < y.col_off;
+        if (x.n != y.n) return x.n > y.n;
+        return x.row_off < y.row_off;
+    });
+    for (uint32_t vi : order1) {
         const VLeaf &v = plan.vleaves[vi];
-        if (v.r <= 0) continue;
         int nl = (v.r + kMaxPhase1Rows - 1) / kMaxPhase1Rows;
         for (int li = 0; li < nl; li++) {
             int l0 = (int)((int64_t)v.r * li / nl), l1 = (int)((int64_t)v.r * (li + 1) / nl);
@@ -429,7 +474,9 @@ static void pack_stages_t(const hmb200_flat &f, const Plan &plan, int phase, siz
             T *tile    = (T *)(pk + d.data_off);
             if (phase == 1) {
                 const Piece1 &p = plan.pieces1[pi];
-                d.out_off = p.out_off; d.nc = (uint16_t)p.nq; d.nr = (uint8_t)p.lr; d.ro = 0;
+                d.out_off = p.out_off; d.nc = (uint16_t)p.nq; d.nr = (uint8_t)p.lr;
+                d.ro  = (uint8_t)(32 / p.lr);                      // column groups G
+                d.pad = (uint16_t)((32768 + p.lr - 1) / p.lr);     // lane / lr == (lane * pad) >> 15 for lane < 32, lr <= 32
                 fill_tile1<T>(f, plan.vleaves[p.vleaf], p, tile);
                 if (((size_t)p.lr * p.nq * sizeof(T)) & 15) std::memset(tile + (size_t)p.lr * p.nq, 0, 8);
             } else {

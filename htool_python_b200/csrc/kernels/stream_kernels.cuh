@@ -26,6 +26,7 @@ struct StreamParams {
     const ZCopy *zcopies;
     const WorkUnit *units;
     uint32_t n_units;
+    uint32_t n_zcopies;
     uint32_t *counter;
     void *xz;               // T*: x | t | partials
     void *y;                // T*: phase-2 output (cluster numbering, or user numbering when out_perm != nullptr)
@@ -68,38 +69,84 @@ __global__ void __launch_bounds__(17 * 32, 1) hmatrix_stream_kernel(const Stream
 
     if (warp == NW) {
         // ============================== producer warp ==============================
+        // All schedule metadata is prefetched so that no global-load latency sits on the per-stage critical path:
+        //   * the NEXT work unit is claimed (atomicAdd) while the current one streams;
+        //   * the 32-byte StageEntry records of a unit are loaded 32 at a time, one per lane, and handed out by shuffles;
+        //   * the ZCopy records live in a 64-entry register window (two coalesced 32-entry loads, the second one in
+        //     flight while the first is consumed).
         const uint64_t pol_stream = ptx::policy_evict_first(); // factor bytes are read exactly once
         const uint64_t pol_vec    = ptx::policy_evict_last();  // x / t slices are re-read by many tiles: keep in L2
         const T *xz = (const T *)p.xz;
+        const uint2 *ztab = reinterpret_cast<const uint2 *>(p.zcopies);
         uint32_t it = 0;
-        while (true) {
-            uint32_t u = 0;
-            if (lane == 0) u = atomicAdd(p.counter, 1u);
-            u = __shfl_sync(0xffffffffu, u, 0);
-            if (u >= p.n_units) break;
-            const WorkUnit wu = p.units[u];
-            for (uint32_t s = wu.first_stage; s < wu.first_stage + wu.n_stages; s++, it++) {
-                const uint4 e0 = __ldg(reinterpret_cast<const uint4 *>(p.stages + s));
-                const uint4 e1 = __ldg(reinterpret_cast<const uint4 *>(p.stages + s) + 1);
-                const uint64_t gmem_off = (uint64_t)e0.x | ((uint64_t)e0.y << 32);
-                const uint32_t bytes = e0.z, z_first = e0.w, n_z = e1.x, z_bytes = e1.y;
-                uint2 zc = make_uint2(0, 0);
-                if ((uint32_t)lane < n_z) zc = __ldg(reinterpret_cast<const uint2 *>(p.zcopies + z_first) + lane);
-                const int slot       = it % NS;
-                const uint32_t par   = (it / NS) & 1u;
-                const uint32_t sbase = ptx::smem_u32(stage_base + (size_t)slot * stage_sz);
-                ptx::mbar_wait(empty_bar(slot), par ^ 1u);
-                if (lane == 0) {
-                    ptx::mbar_arrive_expect_tx(full_bar(slot), bytes + z_bytes);
-                    ptx::bulk_g2s(sbase, p.stream + gmem_off, bytes, full_bar(slot), pol_stream);
+        uint32_t zw = 0xffffffffu; // first ZCopy index held by z_cur (lane l holds zw + l); z_nxt holds zw + 32 + l
+        uint2 z_cur = make_uint2(0, 0), z_nxt = make_uint2(0, 0);
+        auto load_z = [&](uint32_t base) { // coalesced 256 B load, zero beyond the table
+            const uint32_t i = base + lane;
+            return i < p.n_zcopies ? __ldg(ztab + i) : make_uint2(0, 0);
+        };
+        uint32_t u = 0;
+        if (lane == 0) u = atomicAdd(p.counter, 1u);
+        u = __shfl_sync(0xffffffffu, u, 0);
+        while (u < p.n_units) {
+            uint32_t u_next = 0;
+            if (lane == 0) u_next = atomicAdd(p.counter, 1u); // claimed early: its latency hides behind this unit
+            const uint2 wraw = __ldg(reinterpret_cast<const uint2 *>(p.units + u));
+            WorkUnit wu;
+            wu.first_stage = wraw.x;
+            wu.n_stages    = wraw.y;
+            for (uint32_t sb = wu.first_stage; sb < wu.first_stage + wu.n_stages; sb += 32) {
+                const uint32_t cnt = min(32u, wu.first_stage + wu.n_stages - sb);
+                uint4 me0 = make_uint4(0, 0, 0, 0), me1 = make_uint4(0, 0, 0, 0);
+                if ((uint32_t)lane < cnt) {
+                    me0 = __ldg(reinterpret_cast<const uint4 *>(p.stages + sb + lane));
+                    me1 = __ldg(reinterpret_cast<const uint4 *>(p.stages + sb + lane) + 1);
                 }
-                __syncwarp();
-                for (uint32_t i = lane; i < n_z; i += 32) {
-                    if (i >= 32) zc = __ldg(reinterpret_cast<const uint2 *>(p.zcopies + z_first) + i);
-                    const uint32_t zb = zc.y & 0xffffu, zdst = zc.y >> 16;
-                    ptx::bulk_g2s(sbase + p.stage_bytes + zdst, xz + zc.x, zb, full_bar(slot), pol_vec);
+                for (uint32_t j = 0; j < cnt; j++, it++) {
+                    const uint32_t off_lo = __shfl_sync(0xffffffffu, me0.x, j), off_hi = __shfl_sync(0xffffffffu, me0.y, j);
+                    const uint32_t bytes = __shfl_sync(0xffffffffu, me0.z, j), z_first = __shfl_sync(0xffffffffu, me0.w, j);
+                    const uint32_t n_z = __shfl_sync(0xffffffffu, me1.x, j), z_bytes = __shfl_sync(0xffffffffu, me1.y, j);
+                    const uint64_t gmem_off = (uint64_t)off_lo | ((uint64_t)off_hi << 32);
+                    // make the window cover z_first (stages are visited in table order inside a unit, so this is a slide
+                    // by 32 in the common case and a reload after a jump to another unit)
+                    if (n_z) {
+                        if (zw == 0xffffffffu || z_first < zw || z_first >= zw + 64) {
+                            zw    = z_first & ~31u;
+                            z_cur = load_z(zw);
+                            z_nxt = load_z(zw + 32);
+                        } else if (z_first >= zw + 32) {
+                            zw += 32;
+                            z_cur = z_nxt;
+                            z_nxt = load_z(zw + 32);
+                        }
+                    }
+                    const int slot       = it % NS;
+                    const uint32_t par   = (it / NS) & 1u;
+                    const uint32_t sbase = ptx::smem_u32(stage_base + (size_t)slot * stage_sz);
+                    ptx::mbar_wait(empty_bar(slot), par ^ 1u);
+                    if (lane == 0) {
+                        ptx::mbar_arrive_expect_tx(full_bar(slot), bytes + z_bytes);
+                        ptx::bulk_g2s(sbase, p.stream + gmem_off, bytes, full_bar(slot), pol_stream);
+                    }
+                    __syncwarp();
+                    for (uint32_t b = z_first; b < z_first + n_z; b += 32) {
+                        if (b >= zw + 32) { // slide (the chunk [b, b+32) must lie inside [zw, zw+64))
+                            zw += 32;
+                            z_cur = z_nxt;
+                            z_nxt = load_z(zw + 32);
+                        }
+                        const uint32_t rel = b + lane - zw; // < 64
+                        const uint32_t ax = __shfl_sync(0xffffffffu, z_cur.x, rel & 31), ay = __shfl_sync(0xffffffffu, z_cur.y, rel & 31);
+                        const uint32_t bx = __shfl_sync(0xffffffffu, z_nxt.x, rel & 31), by = __shfl_sync(0xffffffffu, z_nxt.y, rel & 31);
+                        const uint32_t zx = rel < 32 ? ax : bx, zy = rel < 32 ? ay : by;
+                        if (b + lane < z_first + n_z) {
+                            const uint32_t zb = zy & 0xffffu, zdst = zy >> 16;
+                            ptx::bulk_g2s(sbase + p.stage_bytes + zdst, xz + zx, zb, full_bar(slot), pol_vec);
+                        }
+                    }
                 }
             }
+            u = __shfl_sync(0xffffffffu, u_next, 0);
         }
         // terminate packet: a header written through the generic proxy, released by a plain arrive
         {
@@ -140,49 +187,70 @@ __global__ void __launch_bounds__(17 * 32, 1) hmatrix_stream_kernel(const Stream
             const int nc        = (int)(d.z >> 16);
             const int nr        = (int)(d.w & 0xffu);
             if (PHASE == 2) {
+                // tile nr x nc (ld nr) at bin rows [ro, ro+nr): lane owns bin rows lane and lane+32
                 const int ro  = (int)((d.w >> 8) & 0xffu);
                 const int i0  = lane - ro, i1 = lane + 32 - ro;
                 const bool a0 = (unsigned)i0 < (unsigned)nr, a1 = (unsigned)i1 < (unsigned)nr;
                 const T *p0   = A + (a0 ? i0 : 0);
                 const T *p1   = A + (a1 ? i1 : 0);
-                T b0 = S::zero(), b1 = S::zero(); // second accumulator pair for ILP
+                T b0 = S::zero(), b1 = S::zero(), c0 = S::zero(), c1 = S::zero(), e0 = S::zero(), e1 = S::zero();
                 int c = 0;
-                for (; c + 2 <= nc; c += 2) {
-                    const T z0 = z[c], z1 = z[c + 1];
-                    const T v00 = a0 ? p0[(size_t)c * nr] : S::zero();
-                    const T v10 = a1 ? p1[(size_t)c * nr] : S::zero();
-                    const T v01 = a0 ? p0[(size_t)(c + 1) * nr] : S::zero();
-                    const T v11 = a1 ? p1[(size_t)(c + 1) * nr] : S::zero();
+                for (; c + 4 <= nc; c += 4) { // 12 shared loads in flight per lane, 4 independent FMA chains per row
+                    const T z0 = z[c], z1 = z[c + 1], z2 = z[c + 2], z3 = z[c + 3];
+                    const T v00 = a0 ? p0[0] : S::zero(), v10 = a1 ? p1[0] : S::zero();
+                    const T v01 = a0 ? p0[nr] : S::zero(), v11 = a1 ? p1[nr] : S::zero();
+                    const T v02 = a0 ? p0[2 * nr] : S::zero(), v12 = a1 ? p1[2 * nr] : S::zero();
+                    const T v03 = a0 ? p0[3 * nr] : S::zero(), v13 = a1 ? p1[3 * nr] : S::zero();
+                    p0 += 4 * nr;
+                    p1 += 4 * nr;
                     S::fma(acc0, v00, z0);
                     S::fma(acc1, v10, z0);
                     S::fma(b0, v01, z1);
                     S::fma(b1, v11, z1);
+                    S::fma(c0, v02, z2);
+                    S::fma(c1, v12, z2);
+                    S::fma(e0, v03, z3);
+                    S::fma(e1, v13, z3);
                 }
-                if (c < nc) {
+                for (; c < nc; c++) {
                     const T z0 = z[c];
-                    const T v00 = a0 ? p0[(size_t)c * nr] : S::zero();
-                    const T v10 = a1 ? p1[(size_t)c * nr] : S::zero();
+                    const T v00 = a0 ? p0[0] : S::zero(), v10 = a1 ? p1[0] : S::zero();
+                    p0 += nr;
+                    p1 += nr;
                     S::fma(acc0, v00, z0);
                     S::fma(acc1, v10, z0);
                 }
-                acc0 = S::add(acc0, b0);
-                acc1 = S::add(acc1, b1);
+                acc0 = S::add(S::add(acc0, b0), S::add(c0, e0));
+                acc1 = S::add(S::add(acc1, b1), S::add(c1, e1));
             } else {
-                // tile lr x nq (ld lr): lane -> (row l = lane % lr, column group g = lane / lr)
+                // tile lr x nq (ld lr): lane = g*lr + l owns row l of the columns k = g, g+G, ...; G = 32 / lr column groups
+                // (G and ceil(32768/lr) come precomputed in the descriptor: no integer division in the kernel)
                 const int lr = nr, nq = nc;
-                const int G  = 32 / lr;
-                const int l  = lane % lr, g = lane / lr;
-                T s0 = S::zero(), s1 = S::zero();
+                const int G  = (int)((d.w >> 8) & 0xffu);
+                const int g  = (int)(((uint32_t)lane * (d.w >> 16)) >> 15);
+                T s0 = S::zero(), s1 = S::zero(), s2 = S::zero(), s3 = S::zero();
                 if (g < G) {
-                    const T *pv = A + l;
+                    const T *pa   = A + lane; // element (l, k=g) sits at g*lr + l = lane
+                    const T *pz   = z + g;
+                    const int sa  = G * lr;
                     int k = g;
-                    for (; k + G < nq; k += 2 * G) {
-                        S::fma(s0, pv[(size_t)k * lr], z[k]);
-                        S::fma(s1, pv[(size_t)(k + G) * lr], z[k + G]);
+                    for (; k + 3 * G < nq; k += 4 * G) {
+                        const T a0 = pa[0], a1 = pa[sa], a2 = pa[2 * sa], a3 = pa[3 * sa];
+                        const T z0 = pz[0], z1 = pz[G], z2 = pz[2 * G], z3 = pz[3 * G];
+                        pa += 4 * sa;
+                        pz += 4 * G;
+                        S::fma(s0, a0, z0);
+                        S::fma(s1, a1, z1);
+                        S::fma(s2, a2, z2);
+                        S::fma(s3, a3, z3);
                     }
-                    if (k < nq) S::fma(s0, pv[(size_t)k * lr], z[k]);
+                    for (; k < nq; k += G) {
+                        S::fma(s0, pa[0], pz[0]);
+                        pa += sa;
+                        pz += G;
+                    }
                 }
-                s0 = S::add(s0, s1);
+                s0 = S::add(S::add(s0, s1), S::add(s2, s3));
                 for (int gg = 1; gg < G; gg++) {
                     const T o = S::shfl(s0, lane < lr ? lane + gg * lr : lane);
                     if (lane < lr) s0 = S::add(s0, o);

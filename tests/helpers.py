@@ -132,7 +132,7 @@ def emulate(flat, op, alpha, x, beta, y, **opts):
                           ctypes.c_void_p(x.ctypes.data), b, ctypes.c_void_p(y.ctypes.data), stats)
     if rc:
         raise RuntimeError(emu.plan_emulate_error().decode())
-    keys = ("stream1_bytes", "stream2_bytes", "pieces1", "pieces2", "stages1", "stages2", "reduce", "bins", "xz_elems", "stored")
+    keys = ("stream1_bytes", "stream2_bytes", "pieces1", "pieces2", "stages1", "stages2", "reduce", "bins", "xz_elems", "stored", "zcopies1", "zcopies2")
     return dict(zip(keys, list(stats)))
 
 

@@ -100,6 +100,7 @@ static void emulate(const hmb200_flat &flat, char op, const Options &opt, T alph
         stats[4] = (int64_t)plan.phase1.stages.size(); stats[5] = (int64_t)plan.phase2.stages.size();
         stats[6] = (int64_t)plan.reduce.size(); stats[7] = (int64_t)plan.bin_start.size() - 1;
         stats[8] = (int64_t)plan.xz_elems; stats[9] = (int64_t)plan.stored_coefficients;
+        stats[10] = (int64_t)plan.phase1.zcopies.size(); stats[11] = (int64_t)plan.phase2.zcopies.size();
     }
 }
 
