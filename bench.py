@@ -32,6 +32,7 @@ import numpy as np  # noqa: E402
 
 METRIC = "H-matvecs/sec (N=1M Laplace 1/r, double, single RHS)"
 UNIT = "matvecs/s"
+WORKLOADS = {"laplace": "Laplace 1/(4 pi r), double,", "helmholtz": "Helmholtz exp(ikr)/(4 pi r), complex<double>,"}
 
 
 def parse():
@@ -44,6 +45,9 @@ def parse():
     ap.add_argument("--eps", type=float, default=1e-3)
     ap.add_argument("--eta", type=float, default=10.0)
     ap.add_argument("--leaf", type=int, default=64)
+    ap.add_argument("--kernel", default="laplace", choices=["laplace", "helmholtz"],
+                    help="laplace = BASELINE.json configs[1] (the metric); helmholtz = configs[2] (complex<double>, off-metric check)")
+    ap.add_argument("--wavenumber", type=float, default=0.0, help="helmholtz: k (default: 10 points per wavelength)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--engine-opts", default="", help="k=v,k=v overrides of hmb200_options (tuning runs)")
     return ap.parse_args()
@@ -79,7 +83,9 @@ def assemble(args, world, rank, log):
     while args.n / 2 ** depth > 46340:
         depth += 1
     depth += 1 if depth else 0  # the builder's depth test is off by one against size = n / 2^depth (measured)
-    H = bridge.build_hmatrix("laplace", tree, epsilon=args.eps, eta=args.eta, target_partition_number=slab,
+    kernel = getattr(args, "kernel", "laplace")
+    k = getattr(args, "wavenumber", 0.0) or 2 * np.pi * np.sqrt(args.n / (4 * np.pi)) / 10.0  # ~10 points per wavelength
+    H = bridge.build_hmatrix(kernel, tree, epsilon=args.eps, eta=args.eta, target_partition_number=slab, wavenumber=k,
                              partition_number_for_symmetry=slab, minimal_target_depth=depth, minimal_source_depth=depth)
     t2 = time.time()
     flat = FlatHMatrix.from_htool(H)
@@ -145,7 +151,8 @@ def run_b200(args):
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     thr, cores = host_threads(world)
-    os.environ.setdefault("OMP_NUM_THREADS", str(thr))
+    if os.environ.get("OMP_NUM_THREADS") in (None, "", "1"):  # torchrun pins it to 1; the host-side assembly wants its share of cores
+        os.environ["OMP_NUM_THREADS"] = str(thr)
     import torch
     import torch.distributed as dist
 
@@ -182,9 +189,12 @@ def run_b200(args):
     n = args.n
     rng = np.random.default_rng(1)
     x_user = rng.random(n)  # U(0,1), seed 1
+    if flat.dtype == "z":
+        x_user = x_user + 1j * rng.random(n)
+    tdt = torch.complex128 if flat.dtype == "z" else torch.float64
     perm_s = flat.source_permutation
     x_cluster = torch.from_numpy(np.ascontiguousarray(x_user[perm_s])).to(dev)
-    y_cluster = torch.zeros(n, dtype=torch.float64, device=dev)
+    y_cluster = torch.zeros(n, dtype=tdt, device=dev)
 
     if world > 1:
         def step():
@@ -233,7 +243,7 @@ def run_b200(args):
 
     # ---- roofline of the dominant kernel (max over ranks of its time; this rank's bytes) ---------------------------
     w1, w2 = w_split(flat)
-    es = 8
+    es = flat.elem_bytes
     alg = {"phase1": es * (w1 + flat.n_cols), "phase2": es * (w2 + flat.n_rows)}
     dom = "phase2" if kms["phase2"] >= kms["phase1"] else "phase1"
     peaks = {}
@@ -243,7 +253,7 @@ def run_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6553.6))
     achieved = alg[dom] / (kms[dom] * 1e-3) / 1e9 if kms[dom] > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": f"hmatrix_stream_kernel<double,{2 if dom == 'phase2' else 1}>", "achieved": round(achieved, 1),
+    roofline = {"bound": "hbm", "kernel": f"hmatrix_stream_kernel<{'double' if es == 8 else 'double2'},{2 if dom == 'phase2' else 1}>", "achieved": round(achieved, 1),
                 "peak": peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback (B200_PROFILING.md)", "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": None, "algorithmic_bytes_per_launch": alg[dom],
                 "kernel_ms": {k: round(v, 4) for k, v in kms.items()},
@@ -260,15 +270,15 @@ def run_b200(args):
     if rank == 0:
         line = {
             "metric": METRIC, "value": round(1e3 / ms_step, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if flat.dtype == "d" else "c128",
             "data": "synthetic",
-            "config": {"workload": f"Laplace 1/(4 pi r) H-matrix, N={n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
-                                   f"leaf {args.leaf}, double, single-RHS matvec (BASELINE.json configs[1])",
+            "config": {"workload": f"{WORKLOADS[args.kernel]} H-matrix, N={n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
+                                   f"leaf {args.leaf}, single-RHS matvec (BASELINE.json configs[{1 if args.kernel == 'laplace' else 2}])",
                        "partition": f"block-row slabs x{world}", "l2": "inputs larger than L2 (factor stream >> 126 MB, read once per step)",
                        "stored_coefficients_rank0": flat.stored_coefficients, "leaves_rank0": flat.n_leaves,
                        "assembly": "reference HMatrixTreeBuilder (OpenMP, native generator), outside the timed region", **build_t},
             "clocks": clocks,
-            "e2e": {"value": round(1.0 / e2e_step, 3), "unit": UNIT, "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * n,
+            "e2e": {"value": round(1.0 / e2e_step, 3), "unit": UNIT, "h2d_bytes_per_step": es * n, "d2h_bytes_per_step": es * n,
                     "ms_per_step": round(e2e_step * 1e3, 4)},
             "gpu_launches": int(launches),
             "roofline": roofline,

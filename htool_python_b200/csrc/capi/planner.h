@@ -11,10 +11,10 @@
 namespace hmb200 {
 
 struct Options {
-    int stage_bytes    = 32768;
+    int stage_bytes    = 49152;
     int stage_z_bytes  = 8192;
-    int n_stages       = 5;
-    int consumer_warps = 8;
+    int n_stages       = 3;
+    int consumer_warps = 16;
     int piece1_bytes   = 8192;
     int piece2_bytes   = 8192;
     int bin_rows       = 64;

@@ -212,13 +212,23 @@ __global__ void __launch_bounds__(17 * 32, 1) hmatrix_stream_kernel(const Stream
                     S::fma(e0, v03, z3);
                     S::fma(e1, v13, z3);
                 }
-                for (; c < nc; c++) {
-                    const T z0 = z[c];
+                if (c + 2 <= nc) {
+                    const T z0 = z[c], z1 = z[c + 1];
                     const T v00 = a0 ? p0[0] : S::zero(), v10 = a1 ? p1[0] : S::zero();
-                    p0 += nr;
-                    p1 += nr;
+                    const T v01 = a0 ? p0[nr] : S::zero(), v11 = a1 ? p1[nr] : S::zero();
+                    p0 += 2 * nr;
+                    p1 += 2 * nr;
                     S::fma(acc0, v00, z0);
                     S::fma(acc1, v10, z0);
+                    S::fma(b0, v01, z1);
+                    S::fma(b1, v11, z1);
+                    c += 2;
+                }
+                if (c < nc) {
+                    const T z0 = z[c];
+                    const T v00 = a0 ? p0[0] : S::zero(), v10 = a1 ? p1[0] : S::zero();
+                    S::fma(c0, v00, z0);
+                    S::fma(c1, v10, z0);
                 }
                 acc0 = S::add(S::add(acc0, b0), S::add(c0, e0));
                 acc1 = S::add(S::add(acc1, b1), S::add(c1, e1));

@@ -56,10 +56,10 @@ typedef struct hmb200_flat {
 
 /* tuning knobs; zero / NULL means default */
 typedef struct hmb200_options {
-    int32_t stage_bytes;     /* bytes of one staged packet in shared memory (default 32768) */
+    int32_t stage_bytes;     /* bytes of one staged packet in shared memory (default 49152) */
     int32_t stage_z_bytes;   /* bytes of the per-stage operand (x / t) area (default 8192) */
-    int32_t n_stages;        /* depth of the TMA ring (default 5) */
-    int32_t consumer_warps;  /* consumer warps per CTA (default 8) */
+    int32_t n_stages;        /* depth of the TMA ring (default 3) */
+    int32_t consumer_warps;  /* consumer warps per CTA (default 16) */
     int32_t piece1_bytes;    /* target bytes of a phase-1 (V) piece (default 8192) */
     int32_t piece2_bytes;    /* max bytes of a phase-2 (U / dense) piece (default 8192) */
     int32_t bin_rows;        /* max rows of a target bin, <= 64 (default 64) */

@@ -1,0 +1,99 @@
+"""Host-side logic of the block-row DistributedOperator path on CPU: world_size-2 `gloo` process group.
+
+The slab product itself is played by the ORACLE here (tests only); what is checked is everything around it that the GPU
+path shares: the reference's row-slab assembly (target_partition_number), slab flattening (offsets relative to the slab
+root), partition displacements, the in-place all-gather of unequal / equal slabs and the two global permutations --
+restating add_distributed_operator_vector_product_global_to_global.hpp:18-118.
+"""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import helpers
+from helpers import TOL, rel_err
+
+pytestmark = pytest.mark.skipif(not helpers.bridge_available(), reason="bridge not built")
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, kernel, n, mu, q):
+    import torch
+    import torch.distributed as dist
+
+    from htool_python_b200 import FlatHMatrix, bridge
+    from htool_python_b200.distributed import allgather_slabs_, partition_displacements
+    from oracle import flat_oracle as fo
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(5)
+        g = rng.standard_normal((3, n))
+        pts = np.asfortranarray(g / np.linalg.norm(g, axis=0))
+        tree = bridge.create_cluster_tree(pts, 2, world, 32)
+        offs, sizes = partition_displacements(tree.partition)
+        assert sum(sizes) == n and len(offs) == world
+        Hp = bridge.build_hmatrix(kernel, tree, epsilon=1e-4, eta=10.0, target_partition_number=rank, partition_number_for_symmetry=rank, wavenumber=3.0)
+        slab = FlatHMatrix.from_htool(Hp)
+        assert slab.n_rows == sizes[rank] and slab.target_offset == offs[rank] and slab.n_cols == n
+        dt = slab.np_dtype
+        X = helpers.rand_vec(rng, n, dt, mu)
+        perm = slab.source_permutation
+        Xc = np.ascontiguousarray(X[perm])                              # global_to_root_cluster (:108)
+        Yc = torch.zeros(n * mu, dtype=torch.from_numpy(np.zeros(1, dt)).dtype)
+        mine = np.zeros((sizes[rank], mu), dtype=dt)
+        fo.add_matrix_product_row_major(slab, "N", 1.0, Xc, 0.0, mine, mu)  # stand-in for the engine's slab product
+        Yc.view(n, mu)[offs[rank]:offs[rank] + sizes[rank]] = torch.from_numpy(mine)
+        allgather_slabs_(Yc, offs, sizes, mu)                           # MPI_Allgatherv (:76)
+        Y = np.empty((n, mu), dtype=dt)
+        Y[slab.target_permutation] = Yc.view(n, mu).numpy()             # root_cluster_to_global (:117)
+        if rank == 0:
+            # the same operator assembled in one piece by the reference, product by the oracle in user numbering
+            tree1 = bridge.create_cluster_tree(pts, 2, 1, 32)
+            H = bridge.build_hmatrix(kernel, tree1, epsilon=1e-4, eta=10.0, wavenumber=3.0)
+            full = FlatHMatrix.from_htool(H)
+            Y_ref = np.stack([fo.matvec_user(full, np.ascontiguousarray(X[:, j])) for j in range(mu)], axis=1)
+            q.put(("ok", rel_err(Y, Y_ref), [int(s) for s in sizes]))
+    except Exception as e:  # pragma: no cover
+        import traceback
+
+        q.put(("error", traceback.format_exc(), None))
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("kernel,n,mu", [("laplace_reg", 3000, 1), ("complex_reg", 2001, 3)])
+def test_block_row_product_two_ranks_gloo(kernel, n, mu):
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, kernel, n, mu, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    status, err, sizes = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+    assert status == "ok", err
+    # two independently compressed operators (slabs vs one piece): agreement to the compression accuracy, not 1e-12
+    assert err < 5e-4, err
+    assert all(p.exitcode == 0 for p in procs)
+
+
+def test_partition_displacements_rejects_gaps():
+    from htool_python_b200.distributed import partition_displacements
+
+    assert partition_displacements([(0, 3), (3, 4)]) == ([0, 3], [3, 4])
+    with pytest.raises(ValueError):
+        partition_displacements([(0, 3), (4, 4)])

@@ -211,3 +211,77 @@ def test_native_assembled_hmatrices(kernel, sym, uplo, n, leaf):
     lhs = e.matvec_user(2.0 * x - 3.0 * x2)
     assert rel_err(lhs, 2.0 * y - 3.0 * e.matvec_user(x2)) < 1e-11
     e.close()
+
+
+def _dist_worker(rank, world, port, q):
+    import os
+
+    import torch
+    import torch.distributed as dist
+
+    from htool_python_b200 import B200DistributedOperator, FlatHMatrix, bridge
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank % torch.cuda.device_count())
+    dist.init_process_group("nccl" if torch.cuda.device_count() >= world else "gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(9)
+        n, mu = 6000, 3
+        g = rng.standard_normal((3, n))
+        pts = np.asfortranarray(g / np.linalg.norm(g, axis=0))
+        tree = bridge.create_cluster_tree(pts, 2, world, 32)
+        Hp = bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-4, eta=10.0, target_partition_number=rank, partition_number_for_symmetry=rank)
+        slab = FlatHMatrix.from_htool(Hp)
+        op = B200DistributedOperator(slab, tree.partition)
+        x = helpers.rand_vec(rng, n, np.float64)
+        X = np.asfortranarray(helpers.rand_vec(rng, n, np.float64, mu))
+        y = op * x
+        Y = op @ X
+        # oracle: every slab's product (each rank restates ALL slabs on the CPU), assembled as the reference driver does
+        offs, sizes = op.offs, op.sizes
+        yb = np.zeros(n)
+        Yb = np.zeros((n, mu))
+        xb, Xb = x[slab.source_permutation], np.ascontiguousarray(X[slab.source_permutation])
+        for p in range(world):
+            Hq = Hp if p == rank else bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-4, eta=10.0, target_partition_number=p, partition_number_for_symmetry=p)
+            fq = FlatHMatrix.from_htool(Hq)
+            out = np.zeros(sizes[p])
+            fo.add_vector_product(fq, "N", 1.0, xb, 0.0, out)
+            yb[offs[p]:offs[p] + sizes[p]] = out
+            outm = np.zeros((sizes[p], mu))
+            fo.add_matrix_product_row_major(fq, "N", 1.0, Xb, 0.0, outm, mu)
+            Yb[offs[p]:offs[p] + sizes[p]] = outm
+        y_ref, Y_ref = np.empty(n), np.empty((n, mu))
+        y_ref[slab.target_permutation] = yb
+        Y_ref[slab.target_permutation] = Yb
+        q.put((rank, rel_err(y, y_ref), rel_err(Y, Y_ref), bool(Y.flags.f_contiguous)))
+        op.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(not helpers.bridge_available(), reason="bridge not built")
+@pytest.mark.parametrize("world", [1, 2])
+def test_distributed_operator(world):
+    """B200DistributedOperator `*` / `@` (user numbering, host arrays) vs the restated block-row driver on the oracle."""
+    import socket
+
+    import torch
+    import torch.multiprocessing as mp
+
+    if world > torch.cuda.device_count():
+        pytest.skip("needs 2 GPUs (NCCL refuses two ranks on one device)")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_dist_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+    for rank, e1, e2, f_order in res:
+        assert e1 < TOL and e2 < TOL and f_order, (rank, e1, e2)
