@@ -89,6 +89,22 @@ V *upload_vec(const std::vector<V> &v, cudaStream_t s) {
     return d;
 }
 
+// host staging copy between the caller's (pageable) vectors and the pinned buffer: multi-threaded above 1 MiB, so that
+// the HOST entry points are not bound by one core's memcpy rate (8 MB vectors at N=1M)
+void staged_copy(void *dst, const void *src, size_t bytes) {
+    constexpr size_t kChunk = 256 << 10;
+    if (bytes < (1u << 20)) {
+        std::memcpy(dst, src, bytes);
+        return;
+    }
+    const int64_t n = (int64_t)((bytes + kChunk - 1) / kChunk);
+#pragma omp parallel for schedule(static) num_threads(8)
+    for (int64_t i = 0; i < n; i++) {
+        const size_t o = (size_t)i * kChunk;
+        std::memcpy((uint8_t *)dst + o, (const uint8_t *)src + o, std::min(kChunk, bytes - o));
+    }
+}
+
 void ensure_pinned(hmb200_handle *h, size_t bytes) {
     if (h->pinned_bytes >= bytes) return;
     if (h->pinned) CUDA_CHECK(cudaFreeHost(h->pinned));
@@ -358,16 +374,16 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
         ensure_pinned(h, in_b + out_b + 64);
         ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out, h->es);
         uint8_t *pin = (uint8_t *)h->pinned, *pout = pin + ((in_b + 63) & ~(size_t)63);
-        std::memcpy(pin, in, in_b);
+        staged_copy(pin, in, in_b);
         CUDA_CHECK(cudaMemcpyAsync(h->xz, pin, in_b, cudaMemcpyHostToDevice, h->stream));
         if (!beta_zero) {
-            std::memcpy(pout, out, out_b);
+            staged_copy(pout, out, out_b);
             CUDA_CHECK(cudaMemcpyAsync(h->ybuf, pout, out_b, cudaMemcpyHostToDevice, h->stream));
         }
         run_product<T>(h, po, alpha, beta, h->ybuf, nullptr);
         CUDA_CHECK(cudaMemcpyAsync(pout, h->ybuf, out_b, cudaMemcpyDeviceToHost, h->stream));
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
-        std::memcpy(out, pout, out_b);
+        staged_copy(out, pout, out_b);
     }
     return 0;
 }
@@ -390,11 +406,11 @@ int matrix_product(hmb200_handle *h, char trans, const double *alpha, const void
         ensure_dev(&h->xbuf, &h->xbuf_elems, (uint64_t)po.n_in * mu, h->es);
         uint8_t *pin = (uint8_t *)h->pinned;
         pout         = pin + ((in_b + 63) & ~(size_t)63);
-        std::memcpy(pin, in, in_b);
+        staged_copy(pin, in, in_b);
         CUDA_CHECK(cudaMemcpyAsync(h->xbuf, pin, in_b, cudaMemcpyHostToDevice, h->stream));
         dout = (T *)h->ybuf + po.n_out; // [column scratch | row-major block]
         if (!beta_zero) {
-            std::memcpy(pout, out, out_b);
+            staged_copy(pout, out, out_b);
             CUDA_CHECK(cudaMemcpyAsync(dout, pout, out_b, cudaMemcpyHostToDevice, h->stream));
         }
         din = (const T *)h->xbuf;
@@ -413,7 +429,7 @@ int matrix_product(hmb200_handle *h, char trans, const double *alpha, const void
     if (mem == HMB200_HOST) {
         CUDA_CHECK(cudaMemcpyAsync(pout, dout, out_b, cudaMemcpyDeviceToHost, h->stream));
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
-        std::memcpy(out, pout, out_b);
+        staged_copy(out, pout, out_b);
     }
     return 0;
 }
@@ -436,7 +452,7 @@ int matvec_user(hmb200_handle *h, const void *x, void *y, int mem, int mu) {
         ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out * mu, h->es);
         uint8_t *pin = (uint8_t *)h->pinned;
         pout         = pin + ((in_b + 63) & ~(size_t)63);
-        std::memcpy(pin, x, in_b);
+        staged_copy(pin, x, in_b);
         CUDA_CHECK(cudaMemcpyAsync(h->xbuf, pin, in_b, cudaMemcpyHostToDevice, h->stream));
         dx = (const T *)h->xbuf;
         dy = (T *)h->ybuf;
@@ -451,7 +467,7 @@ int matvec_user(hmb200_handle *h, const void *x, void *y, int mem, int mu) {
     if (mem == HMB200_HOST) {
         CUDA_CHECK(cudaMemcpyAsync(pout, dy, out_b, cudaMemcpyDeviceToHost, h->stream));
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
-        std::memcpy(y, pout, out_b);
+        staged_copy(y, pout, out_b);
     }
     return 0;
 }
