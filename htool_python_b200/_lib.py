@@ -13,7 +13,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libhmb200.so"
 
 class hmb200_options(ctypes.Structure):
     _fields_ = [(n, c_int32) for n in ("stage_bytes", "stage_z_bytes", "n_stages", "consumer_warps", "piece1_bytes", "piece2_bytes",
-                                       "bin_rows", "unit_stages", "ctas", "build_transpose")] + [("reserved", c_int32 * 6)]
+                                       "bin_rows", "unit_stages", "ctas", "build_transpose", "no_matmat", "stage_z_elems", "mm_stage_bytes", "mm_bin_cols")] + [("reserved", c_int32 * 2)]
 
 
 class hmb200_info(ctypes.Structure):

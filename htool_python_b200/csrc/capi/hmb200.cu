@@ -2,6 +2,7 @@
 #include "hmb200.h"
 #include "planner.h"
 #include "../kernels/stream_kernels.cuh"
+#include "../kernels/mm_kernels.cuh"
 
 #include <chrono>
 #include <cstdio>
@@ -31,18 +32,23 @@ struct PackedOp {
     bool valid = false;
     char op    = 'N';
     int32_t n_in = 0, n_out = 0;
-    uint8_t *stream[2]    = {nullptr, nullptr};
-    StageEntry *stages[2] = {nullptr, nullptr};
-    ZCopy *zcopies[2]     = {nullptr, nullptr};
-    WorkUnit *units[2]    = {nullptr, nullptr};
-    uint32_t n_units[2]   = {0, 0};
-    uint32_t n_zcopies[2] = {0, 0};
+    // index 0: phase 1, 1: phase 2, 2: multi-RHS phase 1 (source-bin grouped V tiles)
+    uint8_t *stream[3]    = {nullptr, nullptr, nullptr};
+    StageEntry *stages[3] = {nullptr, nullptr, nullptr};
+    ZCopy *zcopies[3]     = {nullptr, nullptr, nullptr};
+    WorkUnit *units[3]    = {nullptr, nullptr, nullptr};
+    uint32_t n_units[3]   = {0, 0, 0};
+    uint32_t n_zcopies[3] = {0, 0, 0};
     ReduceSeg *reduce     = nullptr;
     uint32_t n_reduce     = 0;
+    ReduceSeg *reduce_mm  = nullptr;
+    uint32_t n_reduce_mm  = 0;
     uint64_t xz_elems     = 0;
+    uint64_t mm_rows      = 0;
+    bool has_mm           = false;
     // bookkeeping
-    uint64_t stream_bytes[2] = {0, 0};
-    uint64_t n_stages[2] = {0, 0}, n_pieces[2] = {0, 0};
+    uint64_t stream_bytes[3] = {0, 0, 0};
+    uint64_t n_stages[3] = {0, 0, 0}, n_pieces[3] = {0, 0, 0};
     uint64_t table_bytes = 0;
     int n_bins = 0;
 };
@@ -61,6 +67,10 @@ struct hmb200_handle {
     uint64_t xz_elems = 0;
     void *ybuf = nullptr; // device staging for host-resident outputs / user-numbering paths
     uint64_t ybuf_elems = 0;
+    void *ybuf2 = nullptr; // cluster-numbered row-major result of the user-numbering multi-RHS product
+    uint64_t ybuf2_elems = 0;
+    void *ws_mm = nullptr; // multi-RHS workspace rows [x | t | partials] at stride ld (grown on demand)
+    uint64_t ws_mm_elems = 0;
     void *xbuf = nullptr; // device staging for multi-RHS inputs
     uint64_t xbuf_elems = 0;
     void *pinned = nullptr;
@@ -122,7 +132,7 @@ void ensure_dev(void **p, uint64_t *have, uint64_t need_elems, int es) {
 
 // packs one phase's stream window by window through two pinned buffers and uploads it
 void upload_stream(hmb200_handle *h, const hmb200_flat &flat, const Plan &plan, int phase, uint8_t **dptr, double &pack_s, double &up_s) {
-    const PhasePlan &ph = phase == 1 ? plan.phase1 : plan.phase2;
+    const PhasePlan &ph = phase == 1 ? plan.phase1 : (phase == 2 ? plan.phase2 : plan.phase1m);
     CUDA_CHECK(cudaMalloc(dptr, (size_t)std::max<uint64_t>(ph.stream_bytes, 128)));
     if (ph.stages.empty()) return;
     const uint64_t window = std::min<uint64_t>(std::max<uint64_t>(ph.stream_bytes, 1 << 20), 256ull << 20);
@@ -167,8 +177,9 @@ void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) 
     po.n_in  = plan.n_in;
     po.n_out = plan.n_out;
     double pack_s = 0, up_s = 0;
-    for (int ph = 0; ph < 2; ph++) {
-        const PhasePlan &pp = ph == 0 ? plan.phase1 : plan.phase2;
+    po.has_mm = h->opt.build_matmat != 0;
+    for (int ph = 0; ph < (po.has_mm ? 3 : 2); ph++) {
+        const PhasePlan &pp = ph == 0 ? plan.phase1 : (ph == 1 ? plan.phase2 : plan.phase1m);
         upload_stream(h, flat, plan, ph + 1, &po.stream[ph], pack_s, up_s);
         po.stages[ph]       = upload_vec(pp.stages, h->stream);
         po.zcopies[ph]      = upload_vec(pp.zcopies, h->stream);
@@ -181,6 +192,10 @@ void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) 
     }
     po.n_pieces[0] = plan.pieces1.size();
     po.n_pieces[1] = plan.pieces2.size();
+    po.n_pieces[2] = plan.pieces1m.size();
+    po.reduce_mm   = upload_vec(plan.reduce_mm, h->stream);
+    po.n_reduce_mm = (uint32_t)plan.reduce_mm.size();
+    po.mm_rows     = plan.mm_rows;
     po.reduce      = upload_vec(plan.reduce, h->stream);
     po.n_reduce    = (uint32_t)plan.reduce.size();
     po.table_bytes += plan.reduce.size() * sizeof(ReduceSeg);
@@ -197,7 +212,8 @@ void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) 
 }
 
 void free_op(PackedOp &po) {
-    for (int i = 0; i < 2; i++) {
+    cudaFree(po.reduce_mm);
+    for (int i = 0; i < 3; i++) {
         cudaFree(po.stream[i]);
         cudaFree(po.stages[i]);
         cudaFree(po.zcopies[i]);
@@ -211,6 +227,22 @@ template <typename T>
 void set_kernel_attrs(size_t smem1, size_t smem2) {
     CUDA_CHECK(cudaFuncSetAttribute(hmatrix_stream_kernel<T, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
     CUDA_CHECK(cudaFuncSetAttribute(hmatrix_stream_kernel<T, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+}
+
+// workspace row stride for a pass of nc right-hand sides: bank-conflict-free B-fragment loads (mm_kernels.cuh)
+inline int mm_ld(int nc, int es) {
+    const int nc8 = (nc + 7) & ~7;
+    if (es == 16) return nc8 + 2;
+    return nc8 + ((nc8 % 16 == 0) ? 4 : 12);
+}
+inline int mm_max_ld(int es) { return es == 16 ? 34 : 68; }
+
+template <typename T>
+bool mm_fits(const hmb200_handle *h, size_t smem_optin) {
+    const Options &o = h->opt;
+    const int ld = mm_max_ld(h->es);
+    return mm_smem_bytes(1, h->es, o.mm_stage_bytes, 0, 2, o.mm_bin_cols, ld) <= smem_optin &&
+           mm_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_elems, 2, 0, ld) <= smem_optin;
 }
 
 hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, const hmb200_options *opt, int es) {
@@ -236,6 +268,8 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
         while (h->opt.n_stages > 2 && stream_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps) > (size_t)prop.sharedMemPerBlockOptin)
             h->opt.n_stages--;
         h->info = hmb200_info{};
+        if (h->opt.build_matmat && !(es == 8 ? mm_fits<double>(h, prop.sharedMemPerBlockOptin) : mm_fits<double2>(h, prop.sharedMemPerBlockOptin)))
+            h->opt.build_matmat = 0; // packet sizes chosen by the caller leave no room for the multi-RHS kernels' operand rows
         build_op(h, *flat, 'N', h->ops[0]);
         if (h->opt.build_transpose) {
             const char sym = (char)flat->symmetry_for_leaves;
@@ -250,6 +284,17 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
         size_t s1 = stream_smem_bytes(1, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps);
         size_t s2 = stream_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps);
         if (es == 8) set_kernel_attrs<double>(s1, s2); else set_kernel_attrs<double2>(s1, s2);
+        if (h->opt.build_matmat) {
+            const int ldm = mm_max_ld(es);
+            size_t m1 = mm_smem_bytes(1, es, h->opt.mm_stage_bytes, 0, 2, h->opt.mm_bin_cols, ldm), m2 = mm_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_elems, 2, 0, ldm);
+            if (es == 8) {
+                CUDA_CHECK(cudaFuncSetAttribute(hmatrix_mm_kernel<double, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m1));
+                CUDA_CHECK(cudaFuncSetAttribute(hmatrix_mm_kernel<double, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m2));
+            } else {
+                CUDA_CHECK(cudaFuncSetAttribute(hmatrix_mm_kernel<double2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m1));
+                CUDA_CHECK(cudaFuncSetAttribute(hmatrix_mm_kernel<double2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m2));
+            }
+        }
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
         // info
         const PackedOp &n = h->ops[0];
@@ -388,8 +433,73 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
     return 0;
 }
 
-// multi-RHS, row-major blocks.  Round-1 implementation: one streamed product per right-hand side (the factor bytes
-// are re-read mu times); the DMMA leaf-GEMM kernel that streams them once replaces this loop ("matmat").
+// ---- multi-RHS on the DMMA kernels ------------------------------------------------------------------------------
+// Y(:, c0:c0+nc) = beta*Y + alpha*op(A)*X(:, c0:c0+nc) for every pass of <= 64 (32 complex) columns.
+//   x: device; row-major n_in x mu (perm_in == nullptr), or COLUMN-major user block gathered through perm_in
+//   y: device, row-major n_out x mu (stride mu)
+template <typename T>
+void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, const T *x, const int32_t *perm_in, T *y, int mu) {
+    const Options &o = h->opt;
+    const int PC = mm_pass_cols<T>();
+    const int threads = (kMmConsumerWarps + 1) * 32;
+    const int ctas = o.ctas > 0 ? o.ctas : h->n_sms;
+    for (int c0 = 0; c0 < mu; c0 += PC) {
+        const int nc = std::min(PC, mu - c0);
+        const int ld = mm_ld(nc, h->es);
+        ensure_dev(&h->ws_mm, &h->ws_mm_elems, (po.mm_rows + 4) * (uint64_t)mm_max_ld(h->es), h->es);
+        T *ws = (T *)h->ws_mm;
+        {
+            const size_t total = (size_t)po.n_in * nc;
+            const unsigned g = (unsigned)std::min<size_t>((total + 255) / 256 + 1, 148 * 16);
+            if (perm_in) mm_load_rows_kernel<T><<<g, 256, 0, h->stream>>>(x + (size_t)c0 * po.n_in, 0, po.n_in, nc, ws, ld, perm_in, po.n_in);
+            else mm_load_rows_kernel<T><<<g, 256, 0, h->stream>>>(x + c0, mu, po.n_in, nc, ws, ld, nullptr, 0);
+            h->launches++;
+        }
+        CUDA_CHECK(cudaMemsetAsync(h->counters, 0, 64, h->stream));
+        cudaEvent_t *ev = nullptr;
+        if (h->timing) {
+            if (h->ev.empty()) {
+                h->ev.resize(4 * hmb200_handle::kTimingSlots, nullptr);
+                for (auto &e : h->ev) CUDA_CHECK(cudaEventCreate(&e));
+            }
+            ev = h->ev.data() + 4 * (h->timed_products % hmb200_handle::kTimingSlots);
+            h->timed_products++;
+            CUDA_CHECK(cudaEventRecord(ev[0], h->stream));
+        }
+        MmParams p{};
+        p.ws = ws; p.ld = ld; p.ncols = nc; p.y = y + c0; p.ldy = mu;
+        p.alpha_re = alpha[0]; p.alpha_im = h->es == 16 ? alpha[1] : 0.0;
+        p.beta_re  = beta[0];  p.beta_im  = h->es == 16 ? beta[1] : 0.0;
+        p.n_stages = 2; p.z_rows = o.stage_z_elems; p.x_rows = o.mm_bin_cols;
+        if (po.n_units[2] > 0) {
+            p.stream = po.stream[2]; p.stages = po.stages[2]; p.zcopies = po.zcopies[2]; p.units = po.units[2];
+            p.n_units = po.n_units[2]; p.n_zcopies = 0; p.counter = h->counters; p.stage_bytes = o.mm_stage_bytes;
+            size_t smem = mm_smem_bytes(1, h->es, o.mm_stage_bytes, 0, 2, o.mm_bin_cols, ld);
+            hmatrix_mm_kernel<T, 1><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[2]), threads, smem, h->stream>>>(p);
+            h->launches++;
+        }
+        if (ev) CUDA_CHECK(cudaEventRecord(ev[1], h->stream));
+        if (po.n_reduce_mm > 0) {
+            unsigned blocks = std::min<unsigned>((po.n_reduce_mm + 7) / 8, 148 * 32);
+            reduce_rows_kernel<T><<<blocks, 256, 0, h->stream>>>(po.reduce_mm, po.n_reduce_mm, ws, ld, (nc + 7) & ~7);
+            h->launches++;
+        }
+        if (ev) CUDA_CHECK(cudaEventRecord(ev[2], h->stream));
+        if (po.n_units[1] > 0) {
+            p.stream = po.stream[1]; p.stages = po.stages[1]; p.zcopies = po.zcopies[1]; p.units = po.units[1];
+            p.n_units = po.n_units[1]; p.n_zcopies = po.n_zcopies[1]; p.counter = h->counters + 1; p.stage_bytes = o.stage_bytes;
+            size_t smem = mm_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_elems, 2, 0, ld);
+            hmatrix_mm_kernel<T, 2><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]), threads, smem, h->stream>>>(p);
+            h->launches++;
+        }
+        if (ev) CUDA_CHECK(cudaEventRecord(ev[3], h->stream));
+        CUDA_CHECK(cudaGetLastError());
+    }
+}
+
+// multi-RHS, row-major blocks (VirtualGlobalToLocalOperator::add_matrix_product_row_major).  With the multi-RHS stream
+// packed (default) the factors are streamed once per pass of 64 (32 complex) right-hand sides through the DMMA kernels;
+// otherwise (no_matmat) one streamed single-RHS product per column.
 template <typename T>
 int matrix_product(hmb200_handle *h, char trans, const double *alpha, const void *in, const double *beta, void *out, int mu, int mem) {
     CUDA_CHECK(cudaSetDevice(h->device));
@@ -415,15 +525,19 @@ int matrix_product(hmb200_handle *h, char trans, const double *alpha, const void
         }
         din = (const T *)h->xbuf;
     }
-    T *ycol = (T *)h->ybuf;
-    const int tb = 256;
-    const unsigned gin = (unsigned)std::min<size_t>(((size_t)po.n_in + tb - 1) / tb + 1, 4096), gout = (unsigned)std::min<size_t>(((size_t)po.n_out + tb - 1) / tb + 1, 4096);
-    for (int j = 0; j < mu; j++) {
-        strided_gather_kernel<T><<<gin, tb, 0, h->stream>>>(din, po.n_in, mu, j, (T *)h->xz);
-        if (!beta_zero) strided_gather_kernel<T><<<gout, tb, 0, h->stream>>>(dout, po.n_out, mu, j, ycol);
-        run_product<T>(h, po, alpha, beta, ycol, nullptr);
-        strided_scatter_kernel<T><<<gout, tb, 0, h->stream>>>(ycol, po.n_out, mu, j, dout);
-        h->launches += beta_zero ? 2 : 3;
+    if (po.has_mm && mu > 1) {
+        run_mm_product<T>(h, po, alpha, beta, din, nullptr, dout, mu);
+    } else {
+        T *ycol = (T *)h->ybuf;
+        const int tb = 256;
+        const unsigned gin = (unsigned)std::min<size_t>(((size_t)po.n_in + tb - 1) / tb + 1, 4096), gout = (unsigned)std::min<size_t>(((size_t)po.n_out + tb - 1) / tb + 1, 4096);
+        for (int j = 0; j < mu; j++) {
+            strided_gather_kernel<T><<<gin, tb, 0, h->stream>>>(din, po.n_in, mu, j, (T *)h->xz);
+            if (!beta_zero) strided_gather_kernel<T><<<gout, tb, 0, h->stream>>>(dout, po.n_out, mu, j, ycol);
+            run_product<T>(h, po, alpha, beta, ycol, nullptr);
+            strided_scatter_kernel<T><<<gout, tb, 0, h->stream>>>(ycol, po.n_out, mu, j, dout);
+            h->launches += beta_zero ? 2 : 3;
+        }
     }
     CUDA_CHECK(cudaGetLastError());
     if (mem == HMB200_HOST) {
@@ -459,6 +573,16 @@ int matvec_user(hmb200_handle *h, const void *x, void *y, int mem, int mu) {
     }
     const int tb = 256;
     const unsigned gin = (unsigned)std::min<size_t>(((size_t)po.n_in + tb - 1) / tb + 1, 4096);
+    if (po.has_mm && mu > 1) {
+        // column-major user blocks: the permutations and the row-major <-> column-major layout change are fused into the
+        // workspace load and the final store (reference: per-column permutation + 3 transposes, add_hmatrix_matrix_product.hpp:20-90,190-204)
+        ensure_dev(&h->ybuf2, &h->ybuf2_elems, (uint64_t)po.n_out * mu, h->es);
+        T *yc = (T *)h->ybuf2;
+        run_mm_product<T>(h, po, one, zero, dx, h->perm_s, yc, mu);
+        const size_t total = (size_t)po.n_out * mu;
+        mm_store_user_kernel<T><<<(unsigned)std::min<size_t>((total + 255) / 256 + 1, 148 * 16), 256, 0, h->stream>>>(yc, po.n_out, mu, dy, h->perm_t, po.n_out);
+        h->launches++;
+    } else
     for (int j = 0; j < mu; j++) {
         permute_gather_kernel<T><<<gin, tb, 0, h->stream>>>(h->perm_s, 0, po.n_in, dx + (size_t)j * po.n_in, (T *)h->xz, 1);
         h->launches++;
@@ -514,6 +638,8 @@ void hmb200_destroy(hmb200_handle *h) {
     cudaFree(h->xz);
     cudaFree(h->ybuf);
     cudaFree(h->xbuf);
+    cudaFree(h->ws_mm);
+    cudaFree(h->ybuf2);
     cudaFree(h->counters);
     cudaFree(h->perm_t);
     cudaFree(h->perm_s);

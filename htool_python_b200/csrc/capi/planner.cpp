@@ -29,6 +29,10 @@ Options resolve_options(const hmb200_options *o) {
         if (o->unit_stages > 0) r.unit_stages = o->unit_stages;
         if (o->ctas > 0) r.ctas = o->ctas;
         r.build_transpose = o->build_transpose;
+        r.build_matmat    = o->no_matmat ? 0 : 1;
+        if (o->stage_z_elems > 0) r.stage_z_elems = o->stage_z_elems;
+        if (o->mm_stage_bytes > 0) r.mm_stage_bytes = o->mm_stage_bytes;
+        if (o->mm_bin_cols > 0) r.mm_bin_cols = o->mm_bin_cols;
     }
     r.stage_bytes   = (int)align_up((uint32_t)std::max(r.stage_bytes, 2048), 128);
     r.stage_z_bytes = (int)align_up((uint32_t)std::min(std::max(r.stage_z_bytes, 1024), 65536 - 128), 128);
@@ -39,6 +43,9 @@ Options resolve_options(const hmb200_options *o) {
     r.piece1_bytes  = std::min(std::max(r.piece1_bytes, 256), piece_cap);
     r.piece2_bytes  = std::min(std::max(r.piece2_bytes, 256), piece_cap);
     r.unit_stages   = std::max(r.unit_stages, 1);
+    r.stage_z_elems  = std::min(std::max(r.stage_z_elems, 8), 4096);
+    r.mm_stage_bytes = (int)align_up((uint32_t)std::max(r.mm_stage_bytes, 2048), 128);
+    r.mm_bin_cols    = std::min(std::max(r.mm_bin_cols, 4), 4096);
     return r;
 }
 
@@ -155,11 +162,13 @@ struct StageBuilder {
     uint32_t piece_base = 0;
     uint32_t row0 = 0; uint16_t bin_rows = 0, flags = 0;
 
-    StageBuilder(PhasePlan &p, const Options &o, int e) : ph(p), opt(o), es(e) {}
+    StageBuilder(PhasePlan &p, const Options &o, int e) : ph(p), opt(o), es(e), stage_cap((uint32_t)o.stage_bytes), z_cap((uint32_t)o.stage_z_bytes) {}
 
+    uint32_t stage_cap = 0; // packet bytes (opt.stage_bytes, or opt.mm_stage_bytes for the multi-RHS phase-1 stream)
+    uint32_t z_cap     = 0; // operand bytes a packet may reference
     bool fits(uint32_t tile, uint32_t zb) const {
         uint32_t total = 16 + 16 * (n_pieces + 1) + data_bytes + align_up(tile, 16);
-        return total <= (uint32_t)opt.stage_bytes && z_bytes + zb <= (uint32_t)opt.stage_z_bytes && n_pieces < 255;
+        return total <= stage_cap && z_bytes + zb <= z_cap && n_pieces < 255;
     }
     void begin(uint32_t piece_index) {
         first_piece = piece_index; n_pieces = 0; data_bytes = 0; z_bytes = 0; z_first = (uint32_t)ph.zcopies.size();
@@ -204,6 +213,13 @@ struct StageBuilder {
         data_bytes += align_up(tile, 16);
         n_pieces++;
     }
+    // piece whose operand is already resident in shared memory (multi-RHS phase 1): only its row offset is recorded
+    void add_resident(uint32_t tile, uint32_t z_row) {
+        ph.piece_zoff.push_back((uint16_t)z_row);
+        tile_bytes.push_back(align_up(tile, 16));
+        data_bytes += align_up(tile, 16);
+        n_pieces++;
+    }
     static uint32_t z_need(int es, uint32_t z_src, uint32_t z_cnt) {
         uint32_t a, b, c; aligned_span(es, z_src, z_cnt, a, b, c); return b;
     }
@@ -224,6 +240,120 @@ struct StageBuilder {
         piece_base += n_pieces;
     }
 };
+
+// ------------------------------------------------------------------------------------------------------------
+// multi-RHS phase 1: T_j (r x mu) = V_j (r x n) X[cols_j] (n x mu), V tiles grouped by source bin
+// (reference: the first gemm of hmatrix/lrmat/linalg/add_lrmat_matrix_product_row_major.hpp:11-27)
+// ------------------------------------------------------------------------------------------------------------
+static void build_mm_phase1(const Options &opt, Plan &plan) {
+    const int es = plan.elem_bytes;
+    // source bins: <= mm_bin_cols input entries, cut at the leaves' source-cluster boundaries where possible
+    {
+        std::vector<int32_t> cuts{0, plan.n_in};
+        for (const VLeaf &v : plan.vleaves)
+            if (v.r > 0) { cuts.push_back(v.col_off); cuts.push_back(v.col_off + v.n); }
+        std::sort(cuts.begin(), cuts.end());
+        cuts.erase(std::unique(cuts.begin(), cuts.end()), cuts.end());
+        auto &bs = plan.src_bin_start;
+        bs.clear();
+        size_t i = 0;
+        while (i + 1 < cuts.size()) {
+            int s0 = cuts[i];
+            size_t j = i + 1;
+            while (j + 1 < cuts.size() && cuts[j + 1] - s0 <= opt.mm_bin_cols) j++;
+            int e0 = cuts[j];
+            if (e0 - s0 <= opt.mm_bin_cols) bs.push_back(s0);
+            else {
+                int parts = (e0 - s0 + opt.mm_bin_cols - 1) / opt.mm_bin_cols;
+                for (int q = 0; q < parts; q++) bs.push_back(s0 + (int)((int64_t)(e0 - s0) * q / parts));
+            }
+            i = j;
+        }
+        bs.push_back(plan.n_in);
+        if (plan.n_in == 0) bs.assign(1, 0);
+    }
+    const auto &bs   = plan.src_bin_start;
+    const int n_sbin = (int)bs.size() - 1;
+    auto sbin_of = [&](int col) { return (int)(std::upper_bound(bs.begin(), bs.end(), col) - bs.begin()) - 1; };
+    const uint32_t piece_cap = (uint32_t)(opt.mm_stage_bytes - 16 - 16 - 64);
+    uint64_t rows = plan.xz_elems; // partial rows are appended to the matvec workspace rows
+    std::vector<std::pair<int, Piece1>> tmp; // (source bin, piece); z offset (row inside the bin) is k0-derived at pack time
+    for (size_t vi = 0; vi < plan.vleaves.size(); vi++) {
+        const VLeaf &v = plan.vleaves[vi];
+        if (v.r <= 0) continue;
+        const int b0 = sbin_of(v.col_off), b1 = sbin_of(v.col_off + v.n - 1);
+        // column parts: (bin, sub-chunk) pairs; a tile must fit a packet with at least 8 rows
+        struct Part { int b, k0, nq; };
+        std::vector<Part> parts;
+        for (int b = b0; b <= b1; b++) {
+            int cs = std::max(v.col_off, bs[b]), ce = std::min(v.col_off + v.n, bs[b + 1]);
+            if (ce <= cs) continue;
+            int nq_max = std::max(4, (int)(piece_cap / (8u * es)));
+            int nsub   = (ce - cs + nq_max - 1) / nq_max;
+            for (int q = 0; q < nsub; q++) {
+                int k0 = cs + (int)((int64_t)(ce - cs) * q / nsub), k1 = cs + (int)((int64_t)(ce - cs) * (q + 1) / nsub);
+                parts.push_back(Part{b, k0 - v.col_off, k1 - k0});
+            }
+        }
+        int nq_big = 0;
+        for (const Part &pt : parts) nq_big = std::max(nq_big, pt.nq);
+        int lmax = std::min(128, std::max(8, (int)(piece_cap / ((uint32_t)nq_big * es)) / 8 * 8));
+        int nl   = (v.r + lmax - 1) / lmax;
+        for (int li = 0; li < nl; li++) {
+            int l0 = (int)((int64_t)v.r * li / nl), l1 = (int)((int64_t)v.r * (li + 1) / nl), lr = l1 - l0;
+            uint32_t first_partial = 0;
+            if (parts.size() > 1) {
+                first_partial = (uint32_t)rows;
+                plan.reduce_mm.push_back(ReduceSeg{v.t_off + (uint32_t)l0, first_partial, (uint32_t)parts.size(), (uint32_t)lr});
+                rows += (uint64_t)parts.size() * lr;
+            }
+            for (size_t q = 0; q < parts.size(); q++) {
+                Piece1 p{(int32_t)vi, l0, lr, parts[q].k0, parts[q].nq, parts.size() > 1 ? first_partial + (uint32_t)q * lr : v.t_off + (uint32_t)l0};
+                tmp.emplace_back(parts[q].b, p);
+            }
+        }
+    }
+    if (rows >= (1ull << 32)) throw std::runtime_error("multi-RHS workspace exceeds 2^32 rows; split the operator into slabs");
+    plan.mm_rows = rows;
+    std::stable_sort(tmp.begin(), tmp.end(), [](const auto &a, const auto &b) { return a.first < b.first; });
+    plan.pieces1m.resize(tmp.size());
+    for (size_t i = 0; i < tmp.size(); i++) plan.pieces1m[i] = tmp[i].second;
+    // stages: one work unit per source bin; StageEntry.pad = (first x row, rows) of the bin's resident X slice
+    PhasePlan &ph = plan.phase1m;
+    StageBuilder sb(ph, opt, es);
+    sb.stage_cap = (uint32_t)opt.mm_stage_bytes;
+    sb.z_cap     = 0xffffffffu;
+    size_t pi = 0;
+    for (int b = 0; b < n_sbin; b++) {
+        size_t pe = pi;
+        while (pe < tmp.size() && tmp[pe].first == b) pe++;
+        if (pe == pi) continue; // no tile reads this slice of x
+        const uint32_t unit_first = (uint32_t)ph.stages.size();
+        sb.piece_base = 0;
+        sb.row0       = (uint32_t)bs[b];
+        sb.bin_rows   = (uint16_t)(bs[b + 1] - bs[b]);
+        sb.flags      = kFlagFirstOfBin;
+        sb.begin((uint32_t)pi);
+        for (; pi < pe; pi++) {
+            const Piece1 &p = plan.pieces1m[pi];
+            const VLeaf &v  = plan.vleaves[p.vleaf];
+            uint32_t tile   = (uint32_t)p.lr * p.nq * es;
+            if (sb.n_pieces && !sb.fits(tile, 0)) {
+                sb.close();
+                sb.flags = 0;
+                sb.begin((uint32_t)pi);
+            }
+            sb.add_resident(tile, (uint32_t)(v.col_off + p.k0 - bs[b]));
+        }
+        sb.flags |= kFlagLastOfBin;
+        sb.close();
+        for (uint32_t s2 = unit_first; s2 < ph.stages.size(); s2++) {
+            ph.stages[s2].pad[0] = (uint32_t)bs[b];
+            ph.stages[s2].pad[1] = (uint32_t)(bs[b + 1] - bs[b]);
+        }
+        ph.units.push_back(WorkUnit{unit_first, (uint32_t)ph.stages.size() - unit_first});
+    }
+}
 
 // ------------------------------------------------------------------------------------------------------------
 // the plan
@@ -306,6 +436,7 @@ void build_plan(const hmb200_flat &f, int es, char op, const Options &opt, Plan 
                 if (nr <= 0) continue;
                 uint32_t nc_max = std::max<uint32_t>(1, (uint32_t)opt.piece2_bytes / (uint32_t)(nr * es));
                 nc_max          = std::min<uint32_t>(nc_max, std::min<uint32_t>(zmax_elems, 65535u));
+                nc_max          = std::min<uint32_t>(nc_max, (uint32_t)opt.stage_z_elems - 2);
                 int nch         = (int)((K + nc_max - 1) / nc_max);
                 for (int c = 0; c < nch; c++) {
                     int c0 = (int)((int64_t)K * c / nch), c1 = (int)((int64_t)K * (c + 1) / nch);
@@ -355,6 +486,7 @@ void build_plan(const hmb200_flat &f, int es, char op, const Options &opt, Plan 
     {
         PhasePlan &ph = plan.phase2;
         StageBuilder sb(ph, opt, es);
+        sb.z_cap = std::min<uint32_t>(sb.z_cap, (uint32_t)opt.stage_z_elems * es); // the multi-RHS kernel stages operand ROWS
         for (int b = 0; b < n_bins; b++) {
             uint32_t unit_first = (uint32_t)ph.stages.size();
             sb.piece_base       = 0;
@@ -377,6 +509,8 @@ void build_plan(const hmb200_flat &f, int es, char op, const Options &opt, Plan 
             ph.units.push_back(WorkUnit{unit_first, (uint32_t)ph.stages.size() - unit_first});
         }
     }
+    plan.mm_rows = plan.xz_elems;
+    if (opt.build_matmat) build_mm_phase1(opt, plan);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -452,7 +586,7 @@ static void fill_tile1(const hmb200_flat &f, const VLeaf &v, const Piece1 &p, T 
 
 template <typename T>
 static void pack_stages_t(const hmb200_flat &f, const Plan &plan, int phase, size_t s0, size_t s1, uint8_t *dst) {
-    const PhasePlan &ph = phase == 1 ? plan.phase1 : plan.phase2;
+    const PhasePlan &ph = phase == 1 ? plan.phase1 : (phase == 2 ? plan.phase2 : plan.phase1m);
     const uint64_t base = ph.stages[s0].gmem_off;
 #pragma omp parallel for schedule(dynamic, 16)
     for (int64_t s = (int64_t)s0; s < (int64_t)s1; s++) {
@@ -472,8 +606,8 @@ static void pack_stages_t(const hmb200_flat &f, const Plan &plan, int phase, siz
             d.data_off = ph.piece_dataoff[pi];
             d.z_off    = ph.piece_zoff[pi];
             T *tile    = (T *)(pk + d.data_off);
-            if (phase == 1) {
-                const Piece1 &p = plan.pieces1[pi];
+            if (phase == 1 || phase == 3) {
+                const Piece1 &p = phase == 1 ? plan.pieces1[pi] : plan.pieces1m[pi];
                 d.out_off = p.out_off; d.nc = (uint16_t)p.nq; d.nr = (uint8_t)p.lr;
                 d.ro  = (uint8_t)(32 / p.lr);                      // column groups G
                 d.pad = (uint16_t)((32768 + p.lr - 1) / p.lr);     // lane / lr == (lane * pad) >> 15 for lane < 32, lr <= 32

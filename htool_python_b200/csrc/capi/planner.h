@@ -21,6 +21,12 @@ struct Options {
     int unit_stages    = 32;
     int ctas           = 0;
     int build_transpose = 0;
+    // multi-RHS (DMMA) path
+    int build_matmat    = 1;     // also pack the phase-1 stream of the multi-RHS kernels
+    int stage_z_elems   = 112;   // max operand elements (x / t entries) a phase-2 packet may reference: the multi-RHS kernel
+                                 // stages stage_z_elems x (mu + pad) operand ROWS per packet
+    int mm_stage_bytes  = 40960; // packet size of the multi-RHS phase-1 stream
+    int mm_bin_cols     = 128;   // columns of a source bin (the slice of X kept resident in shared memory)
 };
 Options resolve_options(const hmb200_options *opt);
 
@@ -73,6 +79,14 @@ struct Plan {
     std::vector<Piece2> pieces2;
     PhasePlan phase1, phase2;
     std::vector<ReduceSeg> reduce;
+    // multi-RHS phase 1 (T_j = V_j X): V tiles grouped by SOURCE bin; the bin's rows of X stay resident in shared memory
+    // while its tiles stream.  Leaves wider than a bin produce partial T rows (workspace rows >= xz_elems) summed by
+    // reduce_mm; piece_zoff = first row of the tile's columns inside the resident X slice.
+    std::vector<int32_t> src_bin_start; // n_src_bins + 1
+    std::vector<Piece1> pieces1m;
+    PhasePlan phase1m;
+    std::vector<ReduceSeg> reduce_mm;   // in workspace ROWS
+    uint64_t mm_rows = 0;               // workspace rows of the multi-RHS path: [x | t | (matvec partials) | mm partials]
     uint64_t xz_elems = 0; // x | t | partials (+ padding)
     uint32_t t_begin  = 0; // first element of the t region
     double stored_coefficients = 0;

@@ -66,7 +66,13 @@ typedef struct hmb200_options {
     int32_t unit_stages;     /* phase-1 stages per work unit (default 32) */
     int32_t ctas;            /* persistent CTAs (default: number of SMs) */
     int32_t build_transpose; /* also pack the transposed operator so trans='T'/'C' products work (default 0) */
-    int32_t reserved[6];
+    int32_t no_matmat;       /* 1: do not pack the multi-RHS phase-1 stream (saves ~35 % device memory; the multi-RHS
+                                entry points then fall back to one streamed product per right-hand side) */
+    int32_t stage_z_elems;   /* max operand entries (x / t) a phase-2 packet references (default 112); the multi-RHS kernel
+                                stages that many operand ROWS of (mu + pad) per packet */
+    int32_t mm_stage_bytes;  /* packet bytes of the multi-RHS phase-1 stream (default 40960) */
+    int32_t mm_bin_cols;     /* entries of x per source bin, resident in shared memory in multi-RHS phase 1 (default 128) */
+    int32_t reserved[2];
 } hmb200_options;
 
 typedef struct hmb200_handle hmb200_handle;

@@ -104,6 +104,103 @@ static void emulate(const hmb200_flat &flat, char op, const Options &opt, T alph
     }
 }
 
+
+// multi-RHS path: phase-1m packets (source-bin grouped V tiles, resident X rows), reduce_mm, then the phase-2 packets with
+// every operand element widened to a row of mu -- the data flow of kernels/mm_kernels.cuh, on the CPU.
+template <typename T>
+static void emulate_mm(const hmb200_flat &flat, char op, const Options &opt, T alpha, const T *in, T beta, T *out, int mu, int64_t *stats) {
+    const int es = sizeof(T);
+    Plan plan;
+    build_plan(flat, es, op, opt, plan);
+    if (!opt.build_matmat) throw std::runtime_error("plan has no multi-RHS stream");
+    std::vector<T> ws((plan.mm_rows + 4) * (size_t)mu, T(0));
+    std::copy(in, in + (size_t)plan.n_in * mu, ws.begin());
+    {   // phase 1m
+        const PhasePlan &ph = plan.phase1m;
+        std::vector<uint8_t> stream(ph.stream_bytes + 256, 0xAB);
+        if (!ph.stages.empty()) pack_stages(flat, plan, 3, 0, ph.stages.size(), stream.data());
+        for (const WorkUnit &wu : ph.units)
+            for (uint32_t s = wu.first_stage; s < wu.first_stage + wu.n_stages; s++) {
+                const StageEntry &se = ph.stages[s];
+                if (se.bytes > (uint32_t)opt.mm_stage_bytes || (se.bytes & 15) || (se.gmem_off & 15)) throw std::runtime_error("bad mm packet size/alignment");
+                if (se.n_z != 0) throw std::runtime_error("mm phase-1 packet with operand copies");
+                const uint32_t x0 = se.pad[0], xr = se.pad[1];
+                if (xr > (uint32_t)opt.mm_bin_cols || x0 + xr > (uint32_t)plan.n_in) throw std::runtime_error("bad resident X slice");
+                const uint8_t *pk = stream.data() + se.gmem_off;
+                PacketHeader h;
+                std::memcpy(&h, pk, 16);
+                if (h.row0 != x0 || h.bin_rows != xr) throw std::runtime_error("header / stage entry mismatch");
+                for (uint32_t i = 0; i < h.n_pieces; i++) {
+                    PieceDesc d;
+                    std::memcpy(&d, pk + 16 + 16 * (size_t)i, 16);
+                    const T *A = (const T *)(pk + d.data_off);
+                    if (d.data_off + (size_t)d.nr * d.nc * es > se.bytes) throw std::runtime_error("mm tile exceeds packet");
+                    if ((uint32_t)d.z_off + d.nc > xr) throw std::runtime_error("mm tile reads outside the resident X slice");
+                    if ((uint64_t)d.out_off + d.nr > plan.mm_rows) throw std::runtime_error("mm output row out of range");
+                    for (int l = 0; l < d.nr; l++)
+                        for (int j = 0; j < mu; j++) {
+                            T sacc = 0;
+                            for (int k = 0; k < d.nc; k++) sacc += A[(size_t)k * d.nr + l] * ws[(size_t)(x0 + d.z_off + k) * mu + j];
+                            ws[(size_t)(d.out_off + l) * mu + j] = sacc;
+                        }
+                }
+            }
+    }
+    for (const ReduceSeg &rs : plan.reduce_mm)
+        for (uint32_t l = 0; l < rs.len; l++)
+            for (int j = 0; j < mu; j++) {
+                T sacc = 0;
+                for (uint32_t q = 0; q < rs.n_parts; q++) sacc += ws[(size_t)(rs.first_partial + (size_t)q * rs.len + l) * mu + j];
+                ws[(size_t)(rs.final_off + l) * mu + j] = sacc;
+            }
+    {   // phase 2 on the single-RHS stream2, operands as rows
+        const PhasePlan &ph = plan.phase2;
+        std::vector<uint8_t> stream(ph.stream_bytes + 256, 0xAB);
+        if (!ph.stages.empty()) pack_stages(flat, plan, 2, 0, ph.stages.size(), stream.data());
+        std::vector<T> zrows((size_t)opt.stage_z_elems * mu);
+        std::vector<T> acc((size_t)kMaxBinRows * mu);
+        for (const WorkUnit &wu : ph.units) {
+            std::fill(acc.begin(), acc.end(), T(0));
+            for (uint32_t s = wu.first_stage; s < wu.first_stage + wu.n_stages; s++) {
+                const StageEntry &se = ph.stages[s];
+                if (se.z_bytes > (uint32_t)opt.stage_z_elems * es) throw std::runtime_error("phase-2 packet references more operand rows than stage_z_elems");
+                for (uint32_t i = 0; i < se.n_z; i++) {
+                    const ZCopy &zc = ph.zcopies[se.z_first + i];
+                    if ((uint64_t)zc.src_elem + zc.bytes / es > plan.mm_rows + 2) throw std::runtime_error("operand rows out of range");
+                    std::memcpy(zrows.data() + (size_t)(zc.dst_off / es) * mu, ws.data() + (size_t)zc.src_elem * mu, (size_t)(zc.bytes / es) * mu * es);
+                }
+                const uint8_t *pk = stream.data() + se.gmem_off;
+                PacketHeader h;
+                std::memcpy(&h, pk, 16);
+                for (uint32_t i = 0; i < h.n_pieces; i++) {
+                    PieceDesc d;
+                    std::memcpy(&d, pk + 16 + 16 * (size_t)i, 16);
+                    const T *A = (const T *)(pk + d.data_off);
+                    for (int c = 0; c < d.nc; c++)
+                        for (int i2 = 0; i2 < d.nr; i2++)
+                            for (int j = 0; j < mu; j++) acc[(size_t)(d.ro + i2) * mu + j] += A[(size_t)c * d.nr + i2] * zrows[(size_t)(d.z_off + c) * mu + j];
+                }
+                if (h.flags & kFlagLastOfBin) {
+                    for (int r = 0; r < h.bin_rows; r++)
+                        for (int j = 0; j < mu; j++) {
+                            T v = alpha * acc[(size_t)r * mu + j];
+                            if (beta != T(0)) v += beta * out[(size_t)(h.row0 + r) * mu + j];
+                            out[(size_t)(h.row0 + r) * mu + j] = v;
+                        }
+                    std::fill(acc.begin(), acc.end(), T(0));
+                }
+            }
+        }
+    }
+    if (stats) {
+        stats[0] = (int64_t)plan.phase1m.stream_bytes; stats[1] = (int64_t)plan.phase2.stream_bytes;
+        stats[2] = (int64_t)plan.pieces1m.size(); stats[3] = (int64_t)plan.pieces2.size();
+        stats[4] = (int64_t)plan.phase1m.stages.size(); stats[5] = (int64_t)plan.phase2.stages.size();
+        stats[6] = (int64_t)plan.reduce_mm.size(); stats[7] = (int64_t)plan.src_bin_start.size() - 1;
+        stats[8] = (int64_t)plan.mm_rows; stats[9] = (int64_t)plan.stored_coefficients;
+    }
+}
+
 static thread_local std::string g_err;
 
 extern "C" int plan_emulate(const hmb200_flat *flat, int elem_bytes, char op, const hmb200_options *opt, const double *alpha, const void *in, const double *beta, void *out, int64_t *stats) {
@@ -120,3 +217,17 @@ extern "C" int plan_emulate(const hmb200_flat *flat, int elem_bytes, char op, co
     }
 }
 extern "C" const char *plan_emulate_error() { return g_err.c_str(); }
+
+extern "C" int plan_emulate_mm(const hmb200_flat *flat, int elem_bytes, char op, const hmb200_options *opt, const double *alpha, const void *in, const double *beta, void *out, int mu, int64_t *stats) {
+    try {
+        Options o = resolve_options(opt);
+        if (elem_bytes == 8)
+            emulate_mm<double>(*flat, op, o, alpha[0], (const double *)in, beta[0], (double *)out, mu, stats);
+        else
+            emulate_mm<std::complex<double>>(*flat, op, o, {alpha[0], alpha[1]}, (const std::complex<double> *)in, {beta[0], beta[1]}, (std::complex<double> *)out, mu, stats);
+        return 0;
+    } catch (const std::exception &e) {
+        g_err = e.what();
+        return 1;
+    }
+}

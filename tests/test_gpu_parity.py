@@ -285,3 +285,34 @@ def test_distributed_operator(world):
         p.join(timeout=120)
     for rank, e1, e2, f_order in res:
         assert e1 < TOL and e2 < TOL and f_order, (rank, e1, e2)
+
+
+@pytest.mark.parametrize("name,mu", [("d_N_cylinder", 64), ("d_N_rect", 70), ("d_SL_cylinder", 17), ("z_N_sphere", 32), ("z_HL_cylinder", 40), ("z_SL_sphere", 5)])
+def test_multi_rhs_dmma(name, mu):
+    """Y = beta*Y + alpha*op(A)*X on the DMMA kernels (several passes, padded column tails) vs the oracle, and the
+    user-numbering `@` with fused permutations vs the per-column path (no_matmat)."""
+    flat, _ = load_golden(name)
+    rng = np.random.default_rng(mu)
+    e = _engine(flat, build_transpose=1)
+    alpha, beta = (1.25, -0.75) if flat.dtype == "d" else (1.25 - 0.5j, 0.3 + 0.9j)
+    for op in _ops_of(flat):
+        n_in, n_out = (flat.n_cols, flat.n_rows) if op == "N" else (flat.n_rows, flat.n_cols)
+        X = np.ascontiguousarray(helpers.rand_vec(rng, n_in, flat.np_dtype, mu))
+        Y0 = np.ascontiguousarray(helpers.rand_vec(rng, n_out, flat.np_dtype, mu))
+        Y_ref = Y0.copy()
+        fo.add_matrix_product_row_major(flat, op, alpha, X, beta, Y_ref, mu)
+        Y = Y0.copy()
+        e.add_matrix_product_row_major(op, alpha, X, beta, Y, mu)
+        assert rel_err(Y, Y_ref) < TOL, op
+        Yn = np.full_like(Y0, np.nan)  # beta = 0 overwrites
+        e.add_matrix_product_row_major(op, 1.0, X, 0.0, Yn, mu)
+        Y_ref0 = np.zeros_like(Y0)
+        fo.add_matrix_product_row_major(flat, op, 1.0, X, 0.0, Y_ref0, mu)
+        assert rel_err(Yn, Y_ref0) < TOL, op
+    Xu = np.asfortranarray(helpers.rand_vec(rng, flat.n_cols, flat.np_dtype, mu))
+    Yu = e.matmat_user(Xu)
+    e2 = _engine(flat, no_matmat=1)
+    Yu2 = e2.matmat_user(Xu)
+    assert Yu.flags.f_contiguous and rel_err(Yu, Yu2) < TOL
+    e.close()
+    e2.close()

@@ -124,3 +124,47 @@ def test_plan_statistics_and_overhead():
     assert st["stored"] == int(flat.stored_coefficients)
     assert packed >= 8 * flat.stored_coefficients
     assert packed < 1.12 * 8 * flat.stored_coefficients  # tiny leaves (leaf size 16) -> descriptor overhead is at its worst here
+
+
+MM_OPTION_SETS = [
+    {},
+    dict(stage_bytes=8192, stage_z_bytes=1024, stage_z_elems=24, mm_stage_bytes=6144, mm_bin_cols=16, piece2_bytes=1024, bin_rows=20),
+    dict(stage_bytes=4096, stage_z_elems=12, mm_stage_bytes=4096, mm_bin_cols=5, piece2_bytes=512, bin_rows=9),
+]
+
+
+def _check_mm(flat, op, opts, rng, mu):
+    n_in = flat.n_cols if op == "N" else flat.n_rows
+    n_out = flat.n_rows if op == "N" else flat.n_cols
+    alpha, beta = (1.25, -0.75) if flat.dtype == "d" else (1.25 - 0.5j, 0.3 + 0.9j)
+    X = np.ascontiguousarray(helpers.rand_vec(rng, n_in, flat.np_dtype, mu))
+    Y0 = np.ascontiguousarray(helpers.rand_vec(rng, n_out, flat.np_dtype, mu))
+    Y_ref = Y0.copy()
+    fo.add_matrix_product_row_major(flat, op, alpha, X, beta, Y_ref, mu)
+    Y = Y0.copy()
+    stats = helpers.emulate_mm(flat, op, alpha, X, beta, Y, **opts)
+    assert rel_err(Y, Y_ref) < TOL
+    return stats
+
+
+@pytest.mark.parametrize("name", helpers.golden_names())
+@pytest.mark.parametrize("oi", range(len(MM_OPTION_SETS)))
+def test_multi_rhs_streams_reproduce_oracle(name, oi):
+    """the multi-RHS plan (source-bin grouped phase 1, partial rows, operand rows of phase 2) on the golden H-matrices"""
+    flat, _ = load_golden(name)
+    rng = np.random.default_rng(40 + oi)
+    sym = flat.symmetry_for_leaves
+    ops = ["N"] + (["T"] if sym != "H" else []) + (["C"] if flat.dtype == "z" and sym != "S" else [])
+    for op in ops:
+        st = _check_mm(flat, op, MM_OPTION_SETS[oi], rng, mu=3)
+    assert st["src_bins"] >= 1
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_multi_rhs_synthetic_tilings(seed):
+    rng = np.random.default_rng(300 + seed)
+    dtype = "dz"[seed % 2]
+    m, n = int(rng.integers(1, 300)), int(rng.integers(1, 300))
+    flat = synthetic_flat(rng, m, n, dtype=dtype, max_leaf=int(rng.integers(4, 150)), max_rank=int(rng.integers(1, 150)))
+    for opts in MM_OPTION_SETS:
+        _check_mm(flat, "N", opts, rng, mu=int(rng.integers(1, 6)))
