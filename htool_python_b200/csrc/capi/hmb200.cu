@@ -42,6 +42,7 @@ struct PackedOp {
     ReduceSeg *reduce     = nullptr;
     uint32_t n_reduce     = 0;
     ReduceSeg *reduce_mm  = nullptr;
+    uint32_t *reduce_mm_rows = nullptr;
     uint32_t n_reduce_mm  = 0;
     uint64_t xz_elems     = 0;
     uint64_t mm_rows      = 0;
@@ -192,8 +193,9 @@ void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) 
     }
     po.n_pieces[0] = plan.pieces1.size();
     po.n_pieces[1] = plan.pieces2.size();
-    po.n_pieces[2] = plan.pieces1m.size();
+    po.n_pieces[2] = plan.mm_tiles.size();
     po.reduce_mm   = upload_vec(plan.reduce_mm, h->stream);
+    po.reduce_mm_rows = upload_vec(plan.reduce_mm_rows, h->stream);
     po.n_reduce_mm = (uint32_t)plan.reduce_mm.size();
     po.mm_rows     = plan.mm_rows;
     po.reduce      = upload_vec(plan.reduce, h->stream);
@@ -213,6 +215,7 @@ void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) 
 
 void free_op(PackedOp &po) {
     cudaFree(po.reduce_mm);
+    cudaFree(po.reduce_mm_rows);
     for (int i = 0; i < 3; i++) {
         cudaFree(po.stream[i]);
         cudaFree(po.stages[i]);
@@ -481,7 +484,7 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
         if (ev) CUDA_CHECK(cudaEventRecord(ev[1], h->stream));
         if (po.n_reduce_mm > 0) {
             unsigned blocks = std::min<unsigned>((po.n_reduce_mm + 7) / 8, 148 * 32);
-            reduce_rows_kernel<T><<<blocks, 256, 0, h->stream>>>(po.reduce_mm, po.n_reduce_mm, ws, ld, (nc + 7) & ~7);
+            reduce_rows_kernel<T><<<blocks, 256, 0, h->stream>>>(po.reduce_mm, po.reduce_mm_rows, po.n_reduce_mm, ws, ld, (nc + 7) & ~7);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[2], h->stream));

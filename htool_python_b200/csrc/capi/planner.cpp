@@ -276,13 +276,16 @@ static void build_mm_phase1(const Options &opt, Plan &plan) {
     const int n_sbin = (int)bs.size() - 1;
     auto sbin_of = [&](int col) { return (int)(std::upper_bound(bs.begin(), bs.end(), col) - bs.begin()) - 1; };
     const uint32_t piece_cap = (uint32_t)(opt.mm_stage_bytes - 16 - 16 - 64);
-    uint64_t rows = plan.xz_elems; // partial rows are appended to the matvec workspace rows
-    std::vector<std::pair<int, Piece1>> tmp; // (source bin, piece); z offset (row inside the bin) is k0-derived at pack time
+    // rows a tile of nq columns may have: a multiple of 16 (one DMMA row pair per warp item) that fits a packet
+    auto rows_cap = [&](int nq) { return std::min(128, std::max(8, (int)(piece_cap / ((uint32_t)nq * es)) / 16 * 16)); };
+
+    // ---- sub-pieces: (leaf rows l0..l0+lr) x (columns of one source bin, possibly sub-chunked) -----------------------
+    struct Sub { int b; int k_abs; Piece1 p; uint32_t seg; };
+    std::vector<Sub> subs;
     for (size_t vi = 0; vi < plan.vleaves.size(); vi++) {
         const VLeaf &v = plan.vleaves[vi];
         if (v.r <= 0) continue;
         const int b0 = sbin_of(v.col_off), b1 = sbin_of(v.col_off + v.n - 1);
-        // column parts: (bin, sub-chunk) pairs; a tile must fit a packet with at least 8 rows
         struct Part { int b, k0, nq; };
         std::vector<Part> parts;
         for (int b = b0; b <= b1; b++) {
@@ -297,53 +300,82 @@ static void build_mm_phase1(const Options &opt, Plan &plan) {
         }
         int nq_big = 0;
         for (const Part &pt : parts) nq_big = std::max(nq_big, pt.nq);
-        int lmax = std::min(128, std::max(8, (int)(piece_cap / ((uint32_t)nq_big * es)) / 8 * 8));
-        int nl   = (v.r + lmax - 1) / lmax;
+        const int lmax = rows_cap(nq_big);
+        const int nl   = (v.r + lmax - 1) / lmax;
         for (int li = 0; li < nl; li++) {
             int l0 = (int)((int64_t)v.r * li / nl), l1 = (int)((int64_t)v.r * (li + 1) / nl), lr = l1 - l0;
-            uint32_t first_partial = 0;
-            if (parts.size() > 1) {
-                first_partial = (uint32_t)rows;
-                plan.reduce_mm.push_back(ReduceSeg{v.t_off + (uint32_t)l0, first_partial, (uint32_t)parts.size(), (uint32_t)lr});
-                rows += (uint64_t)parts.size() * lr;
-            }
-            for (size_t q = 0; q < parts.size(); q++) {
-                Piece1 p{(int32_t)vi, l0, lr, parts[q].k0, parts[q].nq, parts.size() > 1 ? first_partial + (uint32_t)q * lr : v.t_off + (uint32_t)l0};
-                tmp.emplace_back(parts[q].b, p);
-            }
+            const uint32_t seg = (uint32_t)plan.reduce_mm.size();
+            plan.reduce_mm.push_back(ReduceSeg{v.t_off + (uint32_t)l0, 0, 0, (uint32_t)lr});
+            for (const Part &pt : parts) subs.push_back(Sub{pt.b, v.col_off + pt.k0, Piece1{(int32_t)vi, l0, lr, pt.k0, pt.nq, 0}, seg});
         }
+    }
+    // same (bin, column range) => neighbours: they are stacked into one tile
+    std::stable_sort(subs.begin(), subs.end(), [](const Sub &x, const Sub &y) {
+        if (x.b != y.b) return x.b < y.b;
+        if (x.k_abs != y.k_abs) return x.k_abs < y.k_abs;
+        return x.p.nq > y.p.nq;
+    });
+    // ---- tiles: stacks of sub-pieces sharing their columns; every tile writes a contiguous block of workspace rows ---
+    uint64_t rows = plan.xz_elems;
+    plan.pieces1m.resize(subs.size());
+    std::vector<int> tile_bin;
+    std::vector<std::vector<uint32_t>> seg_rows(plan.reduce_mm.size());
+    for (size_t i = 0; i < subs.size();) {
+        MmTile t{};
+        t.first_sub = (uint32_t)i;
+        t.nq        = (uint16_t)subs[i].p.nq;
+        t.zrow      = (uint16_t)(subs[i].k_abs - bs[subs[i].b]);
+        t.out_row   = (uint32_t)rows;
+        const int cap = rows_cap(subs[i].p.nq);
+        int r = 0;
+        size_t j = i;
+        while (j < subs.size() && subs[j].b == subs[i].b && subs[j].k_abs == subs[i].k_abs && subs[j].p.nq == subs[i].p.nq && (r == 0 || r + subs[j].p.lr <= cap)) {
+            Piece1 p  = subs[j].p;
+            p.out_off = (uint32_t)(rows + r);
+            plan.pieces1m[j] = p;
+            seg_rows[subs[j].seg].push_back(p.out_off);
+            r += p.lr;
+            j++;
+        }
+        t.n_sub = (uint32_t)(j - i);
+        t.rows  = (uint16_t)r;
+        rows += (uint64_t)r;
+        plan.mm_tiles.push_back(t);
+        tile_bin.push_back(subs[i].b);
+        i = j;
     }
     if (rows >= (1ull << 32)) throw std::runtime_error("multi-RHS workspace exceeds 2^32 rows; split the operator into slabs");
     plan.mm_rows = rows;
-    std::stable_sort(tmp.begin(), tmp.end(), [](const auto &a, const auto &b) { return a.first < b.first; });
-    plan.pieces1m.resize(tmp.size());
-    for (size_t i = 0; i < tmp.size(); i++) plan.pieces1m[i] = tmp[i].second;
-    // stages: one work unit per source bin; StageEntry.pad = (first x row, rows) of the bin's resident X slice
+    for (size_t sg = 0; sg < plan.reduce_mm.size(); sg++) {
+        plan.reduce_mm[sg].first_partial = (uint32_t)plan.reduce_mm_rows.size();
+        plan.reduce_mm[sg].n_parts       = (uint32_t)seg_rows[sg].size();
+        plan.reduce_mm_rows.insert(plan.reduce_mm_rows.end(), seg_rows[sg].begin(), seg_rows[sg].end());
+    }
+    // ---- stages: one work unit per source bin; StageEntry.pad = (first x row, rows) of the bin's resident X slice ----
     PhasePlan &ph = plan.phase1m;
     StageBuilder sb(ph, opt, es);
     sb.stage_cap = (uint32_t)opt.mm_stage_bytes;
     sb.z_cap     = 0xffffffffu;
-    size_t pi = 0;
+    size_t ti = 0;
     for (int b = 0; b < n_sbin; b++) {
-        size_t pe = pi;
-        while (pe < tmp.size() && tmp[pe].first == b) pe++;
-        if (pe == pi) continue; // no tile reads this slice of x
+        size_t te = ti;
+        while (te < plan.mm_tiles.size() && tile_bin[te] == b) te++;
+        if (te == ti) continue; // no tile reads this slice of x
         const uint32_t unit_first = (uint32_t)ph.stages.size();
         sb.piece_base = 0;
         sb.row0       = (uint32_t)bs[b];
         sb.bin_rows   = (uint16_t)(bs[b + 1] - bs[b]);
         sb.flags      = kFlagFirstOfBin;
-        sb.begin((uint32_t)pi);
-        for (; pi < pe; pi++) {
-            const Piece1 &p = plan.pieces1m[pi];
-            const VLeaf &v  = plan.vleaves[p.vleaf];
-            uint32_t tile   = (uint32_t)p.lr * p.nq * es;
+        sb.begin((uint32_t)ti);
+        for (; ti < te; ti++) {
+            const MmTile &t = plan.mm_tiles[ti];
+            uint32_t tile   = (uint32_t)t.rows * t.nq * es;
             if (sb.n_pieces && !sb.fits(tile, 0)) {
                 sb.close();
                 sb.flags = 0;
-                sb.begin((uint32_t)pi);
+                sb.begin((uint32_t)ti);
             }
-            sb.add_resident(tile, (uint32_t)(v.col_off + p.k0 - bs[b]));
+            sb.add_resident(tile, t.zrow);
         }
         sb.flags |= kFlagLastOfBin;
         sb.close();
@@ -564,23 +596,23 @@ static void fill_tile2(const hmb200_flat &f, const VLeaf &v, const Piece2 &p, T 
 }
 
 template <typename T>
-static void fill_tile1(const hmb200_flat &f, const VLeaf &v, const Piece1 &p, T *dst) {
+static void fill_tile1(const hmb200_flat &f, const VLeaf &v, const Piece1 &p, T *dst, int ld) {
     const int64_t l = v.leaf;
     const int r = v.r;
     if (!v.transposed) { // V: r x n, ld r
         const T *V = (const T *)f.b[l];
-        if (p.lr == r && p.l0 == 0) {
+        if (p.lr == r && p.l0 == 0 && ld == r) {
             std::memcpy(dst, V + (size_t)p.k0 * r, sizeof(T) * (size_t)r * p.nq);
         } else {
             for (int k = 0; k < p.nq; k++)
-                std::memcpy(dst + (size_t)k * p.lr, V + (size_t)(p.k0 + k) * r + p.l0, sizeof(T) * p.lr);
+                std::memcpy(dst + (size_t)k * ld, V + (size_t)(p.k0 + k) * r + p.l0, sizeof(T) * p.lr);
         }
     } else { // V-role is U^T (r x m_leaf): view(l, k) = U(k, l)
         const T *U = (const T *)f.a[l];
         const int lm = f.nrows[l];
         for (int k = 0; k < p.nq; k++)
             for (int ll = 0; ll < p.lr; ll++)
-                dst[(size_t)k * p.lr + ll] = conj_if(U[(size_t)(p.l0 + ll) * lm + (p.k0 + k)], v.conj);
+                dst[(size_t)k * ld + ll] = conj_if(U[(size_t)(p.l0 + ll) * lm + (p.k0 + k)], v.conj);
     }
 }
 
@@ -606,13 +638,23 @@ static void pack_stages_t(const hmb200_flat &f, const Plan &plan, int phase, siz
             d.data_off = ph.piece_dataoff[pi];
             d.z_off    = ph.piece_zoff[pi];
             T *tile    = (T *)(pk + d.data_off);
-            if (phase == 1 || phase == 3) {
-                const Piece1 &p = phase == 1 ? plan.pieces1[pi] : plan.pieces1m[pi];
+            if (phase == 1) {
+                const Piece1 &p = plan.pieces1[pi];
                 d.out_off = p.out_off; d.nc = (uint16_t)p.nq; d.nr = (uint8_t)p.lr;
                 d.ro  = (uint8_t)(32 / p.lr);                      // column groups G
                 d.pad = (uint16_t)((32768 + p.lr - 1) / p.lr);     // lane / lr == (lane * pad) >> 15 for lane < 32, lr <= 32
-                fill_tile1<T>(f, plan.vleaves[p.vleaf], p, tile);
+                fill_tile1<T>(f, plan.vleaves[p.vleaf], p, tile, p.lr);
                 if (((size_t)p.lr * p.nq * sizeof(T)) & 15) std::memset(tile + (size_t)p.lr * p.nq, 0, 8);
+            } else if (phase == 3) { // multi-RHS phase 1: a stack of sub-pieces sharing their columns, ld = total rows
+                const MmTile &t = plan.mm_tiles[pi];
+                d.out_off = t.out_row; d.nc = t.nq; d.nr = (uint8_t)t.rows; d.ro = 0; d.pad = 0;
+                int roff = 0;
+                for (uint32_t q = 0; q < t.n_sub; q++) {
+                    const Piece1 &p = plan.pieces1m[t.first_sub + q];
+                    fill_tile1<T>(f, plan.vleaves[p.vleaf], p, tile + roff, t.rows);
+                    roff += p.lr;
+                }
+                if (((size_t)t.rows * t.nq * sizeof(T)) & 15) std::memset(tile + (size_t)t.rows * t.nq, 0, 8);
             } else {
                 const Piece2 &p = plan.pieces2[pi];
                 d.out_off = 0; d.nc = (uint16_t)p.nc; d.nr = (uint8_t)p.nr; d.ro = (uint8_t)p.ro;

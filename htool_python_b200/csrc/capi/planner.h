@@ -52,6 +52,12 @@ struct Piece2 { // U-role / dense tile rows [r0,r0+nr) x cols [c0,c0+nc) of the 
     uint32_t z_src; // xz element the tile's first column multiplies
 };
 
+struct MmTile { // multi-RHS phase-1 tile: sub-pieces [first_sub, first_sub + n_sub) of pieces1m stacked row-wise
+    uint32_t first_sub, n_sub;
+    uint32_t out_row; // first workspace row of its `rows` output rows
+    uint16_t rows, nq, zrow;
+};
+
 struct StageHost { // planner-side description of a packet
     uint32_t first_piece, n_pieces;
     uint32_t piece_base;
@@ -83,7 +89,9 @@ struct Plan {
     // while its tiles stream.  Leaves wider than a bin produce partial T rows (workspace rows >= xz_elems) summed by
     // reduce_mm; piece_zoff = first row of the tile's columns inside the resident X slice.
     std::vector<int32_t> src_bin_start; // n_src_bins + 1
-    std::vector<Piece1> pieces1m;
+    std::vector<Piece1> pieces1m;        // sub-pieces; out_off = workspace row of the sub-piece's first output row
+    std::vector<MmTile> mm_tiles;        // the packed tiles (the `pieces` of phase1m)
+    std::vector<uint32_t> reduce_mm_rows; // part rows of the segments: seg.first_partial indexes this array
     PhasePlan phase1m;
     std::vector<ReduceSeg> reduce_mm;   // in workspace ROWS
     uint64_t mm_rows = 0;               // workspace rows of the multi-RHS path: [x | t | (matvec partials) | mm partials]

@@ -56,7 +56,7 @@ __host__ __device__ inline size_t mm_smem_bytes(int phase, int elem_bytes, int s
 }
 
 __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
 // accumulators of one warp: MT m-tiles x NT n-tiles (x re/im)
@@ -79,46 +79,57 @@ struct MmAcc {
 //   B: row-major operand rows (ld = ldb), row k, column c_base + 8*nt + gid
 template <typename T, int NT>
 __device__ __forceinline__ void mm_tile(MmAcc<T, 2, NT> &acc, const T *A, int lda, int nr, int r_base, const T *B, int ldb, int c_base, int nk, int lane) {
+    using S = Scalar<T>;
     const int gid = lane >> 2, tig = lane & 3;
     const int r0 = r_base + gid, r1 = r_base + 8 + gid;
     const bool v0 = (unsigned)r0 < (unsigned)nr, v1 = (unsigned)r1 < (unsigned)nr;
     const T *a0p = A + (v0 ? r0 : 0) + (size_t)tig * lda;
     const T *a1p = A + (v1 ? r1 : 0) + (size_t)tig * lda;
     const T *bp  = B + (size_t)tig * ldb + c_base + gid;
-    for (int k0 = 0; k0 < nk; k0 += 4) {
-        const bool kv = k0 + tig < nk; // zero-fill the K tail: neighbouring bytes are other tiles / headers
-        if constexpr (sizeof(T) == 8) {
-            const double a0 = (kv && v0) ? a0p[0] : 0.0, a1 = (kv && v1) ? a1p[0] : 0.0;
-            double b[NT];
+    // fragments of the current k-step; the next step's are loaded before the DMMAs of this one are issued
+    // (the K tail is zero-filled: the bytes next to a tile are other tiles / headers)
+    T a0, a1, b[NT];
+    {
+        const bool kv = tig < nk;
+        a0 = (kv && v0) ? a0p[0] : S::zero();
+        a1 = (kv && v1) ? a1p[0] : S::zero();
 #pragma unroll
-            for (int j = 0; j < NT; j++) b[j] = kv ? bp[8 * j] : 0.0;
+        for (int j = 0; j < NT; j++) b[j] = kv ? bp[8 * j] : S::zero();
+    }
+    for (int k0 = 0; k0 < nk; k0 += 4) {
+        a0p += 4 * (size_t)lda;
+        a1p += 4 * (size_t)lda;
+        bp += 4 * (size_t)ldb;
+        const bool kv = k0 + 4 + tig < nk;
+        const T na0 = (kv && v0) ? a0p[0] : S::zero();
+        const T na1 = (kv && v1) ? a1p[0] : S::zero();
+        T nb[NT];
+#pragma unroll
+        for (int j = 0; j < NT; j++) nb[j] = kv ? bp[8 * j] : S::zero();
+        if constexpr (sizeof(T) == 8) {
 #pragma unroll
             for (int j = 0; j < NT; j++) {
                 dmma884(acc.v[0][j][0][0], acc.v[0][j][0][1], a0, b[j]);
                 dmma884(acc.v[1][j][0][0], acc.v[1][j][0][1], a1, b[j]);
             }
         } else {
-            const double2 z = make_double2(0.0, 0.0);
-            const double2 a0 = (kv && v0) ? a0p[0] : z, a1 = (kv && v1) ? a1p[0] : z;
-            double2 b[NT];
-#pragma unroll
-            for (int j = 0; j < NT; j++) b[j] = kv ? bp[8 * j] : z;
 #pragma unroll
             for (int j = 0; j < NT; j++) {
                 // (ar + i ai)(br + i bi): re += ar br - ai bi ; im += ar bi + ai br
                 dmma884(acc.v[0][j][0][0], acc.v[0][j][0][1], a0.x, b[j].x);
-                dmma884(acc.v[0][j][0][0], acc.v[0][j][0][1], -a0.y, b[j].y);
                 dmma884(acc.v[0][j][1][0], acc.v[0][j][1][1], a0.x, b[j].y);
-                dmma884(acc.v[0][j][1][0], acc.v[0][j][1][1], a0.y, b[j].x);
                 dmma884(acc.v[1][j][0][0], acc.v[1][j][0][1], a1.x, b[j].x);
-                dmma884(acc.v[1][j][0][0], acc.v[1][j][0][1], -a1.y, b[j].y);
                 dmma884(acc.v[1][j][1][0], acc.v[1][j][1][1], a1.x, b[j].y);
+                dmma884(acc.v[0][j][0][0], acc.v[0][j][0][1], -a0.y, b[j].y);
+                dmma884(acc.v[0][j][1][0], acc.v[0][j][1][1], a0.y, b[j].x);
+                dmma884(acc.v[1][j][0][0], acc.v[1][j][0][1], -a1.y, b[j].y);
                 dmma884(acc.v[1][j][1][0], acc.v[1][j][1][1], a1.y, b[j].x);
             }
         }
-        a0p += 4 * (size_t)lda;
-        a1p += 4 * (size_t)lda;
-        bp += 4 * (size_t)ldb;
+        a0 = na0;
+        a1 = na1;
+#pragma unroll
+        for (int j = 0; j < NT; j++) b[j] = nb[j];
     }
 }
 
@@ -289,32 +300,35 @@ __global__ void __launch_bounds__((kMmConsumerWarps + 1) * 32, 1) hmatrix_mm_ker
                 ptx::mbar_wait(xfull_bar(buf), (ul >> 1) & 1u);
                 xres = reinterpret_cast<const T *>(x_base + (size_t)buf * x_bytes);
             }
+            // work items = (tile, 16-row pair, column quarter): equal-sized, dealt round-robin to the consumer warps
+            constexpr int NQ = NT / 2; // n-tiles per item (2 real / 1 complex): a quarter of the pass's columns
             uint32_t item = 0;
             for (uint32_t i = 0; i < n_pieces; i++) {
                 const uint4 d = *reinterpret_cast<const uint4 *>(pk + 16 + 16 * i);
                 const int nq = (int)(d.z >> 16), lr = (int)(d.w & 0xffu);
                 const int n_mp = (lr + 15) >> 4;
-                for (int q = 0; q < 2 * n_mp; q++, item++) {
+                for (int q = 0; q < 4 * n_mp; q++, item++) {
                     if ((int)(item % NW) != warp) continue;
-                    const int mp = q >> 1, cb = (q & 1) * NT * 8;
+                    const int mp = q >> 2, cb = (q & 3) * NQ * 8;
                     if (cb >= ncols8) continue;
                     const T *A = reinterpret_cast<const T *>(pk + d.x);
-                    acc.clear();
-                    mm_tile<T, NT>(acc, A, lr, lr, 16 * mp, xres + (size_t)(d.z & 0xffffu) * ld, ld, cb, nq, lane);
+                    MmAcc<T, 2, NQ> a1;
+                    a1.clear();
+                    mm_tile<T, NQ>(a1, A, lr, lr, 16 * mp, xres + (size_t)(d.z & 0xffffu) * ld, ld, cb, nq, lane);
 #pragma unroll
                     for (int mt = 0; mt < 2; mt++) {
                         const int r = 16 * mp + 8 * mt + gid;
                         if (r < lr) {
                             T *orow = ws + (size_t)(d.y + r) * ld;
 #pragma unroll
-                            for (int j = 0; j < NT; j++) {
+                            for (int j = 0; j < NQ; j++) {
                                 const int col = cb + 8 * j + 2 * tig;
                                 if (col < ncols8) {
                                     if constexpr (sizeof(T) == 8) {
-                                        *reinterpret_cast<double2 *>(orow + col) = make_double2(acc.v[mt][j][0][0], acc.v[mt][j][0][1]);
+                                        *reinterpret_cast<double2 *>(orow + col) = make_double2(a1.v[mt][j][0][0], a1.v[mt][j][0][1]);
                                     } else {
-                                        orow[col]     = make_double2(acc.v[mt][j][0][0], acc.v[mt][j][1][0]);
-                                        orow[col + 1] = make_double2(acc.v[mt][j][0][1], acc.v[mt][j][1][1]);
+                                        orow[col]     = make_double2(a1.v[mt][j][0][0], a1.v[mt][j][1][0]);
+                                        orow[col + 1] = make_double2(a1.v[mt][j][0][1], a1.v[mt][j][1][1]);
                                     }
                                 }
                             }
@@ -332,21 +346,28 @@ __global__ void __launch_bounds__((kMmConsumerWarps + 1) * 32, 1) hmatrix_mm_ker
     }
 }
 
-// final T rows = sum of the partial rows of leaves that span several source bins (deterministic order)
+// final T rows = sum of the output rows phase 1 wrote for the parts (source bins) of each leaf, in a fixed order
+// (also the plain copy into the t slot for a leaf with one part); one warp per segment, lanes over (row, column pairs)
 template <typename T>
-__global__ void __launch_bounds__(256) reduce_rows_kernel(const ReduceSeg *segs, uint32_t n_segs, T *ws, int ld, int ncols8) {
-    using S = Scalar<T>;
-    // one warp per (segment, row); lanes over columns
+__global__ void __launch_bounds__(256) reduce_rows_kernel(const ReduceSeg *segs, const uint32_t *part_rows, uint32_t n_segs, T *ws, int ld, int ncols8) {
     const uint32_t wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
     const int lane = threadIdx.x & 31;
+    constexpr int V = sizeof(T) == 8 ? 2 : 1; // elements per 16-byte access
+    const int cpr   = ncols8 / V;              // 16-byte chunks per row
     for (uint32_t sidx = wid; sidx < n_segs; sidx += nw) {
         const uint4 sg = __ldg(reinterpret_cast<const uint4 *>(segs + sidx));
-        for (uint32_t l = 0; l < sg.w; l++)
-            for (int c = lane; c < ncols8; c += 32) {
-                T s = S::zero();
-                for (uint32_t q = 0; q < sg.z; q++) s = S::add(s, ws[(size_t)(sg.y + (size_t)q * sg.w + l) * ld + c]);
-                ws[(size_t)(sg.x + l) * ld + c] = s;
+        const int total = (int)sg.w * cpr;
+        for (int e = lane; e < total; e += 32) {
+            const int l = e / cpr, c = (e - l * cpr) * V;
+            double2 s = make_double2(0.0, 0.0);
+            for (uint32_t q = 0; q < sg.z; q++) {
+                const uint32_t row = __ldg(part_rows + sg.y + q) + l;
+                const double2 v    = *reinterpret_cast<const double2 *>(ws + (size_t)row * ld + c);
+                s.x += v.x;
+                s.y += v.y;
             }
+            *reinterpret_cast<double2 *>(ws + (size_t)(sg.x + l) * ld + c) = s;
+        }
     }
 }
 

@@ -150,7 +150,7 @@ static void emulate_mm(const hmb200_flat &flat, char op, const Options &opt, T a
         for (uint32_t l = 0; l < rs.len; l++)
             for (int j = 0; j < mu; j++) {
                 T sacc = 0;
-                for (uint32_t q = 0; q < rs.n_parts; q++) sacc += ws[(size_t)(rs.first_partial + (size_t)q * rs.len + l) * mu + j];
+                for (uint32_t q = 0; q < rs.n_parts; q++) sacc += ws[(size_t)(plan.reduce_mm_rows[rs.first_partial + q] + l) * mu + j];
                 ws[(size_t)(rs.final_off + l) * mu + j] = sacc;
             }
     {   // phase 2 on the single-RHS stream2, operands as rows
@@ -194,7 +194,7 @@ static void emulate_mm(const hmb200_flat &flat, char op, const Options &opt, T a
     }
     if (stats) {
         stats[0] = (int64_t)plan.phase1m.stream_bytes; stats[1] = (int64_t)plan.phase2.stream_bytes;
-        stats[2] = (int64_t)plan.pieces1m.size(); stats[3] = (int64_t)plan.pieces2.size();
+        stats[2] = (int64_t)plan.mm_tiles.size(); stats[3] = (int64_t)plan.pieces2.size();
         stats[4] = (int64_t)plan.phase1m.stages.size(); stats[5] = (int64_t)plan.phase2.stages.size();
         stats[6] = (int64_t)plan.reduce_mm.size(); stats[7] = (int64_t)plan.src_bin_start.size() - 1;
         stats[8] = (int64_t)plan.mm_rows; stats[9] = (int64_t)plan.stored_coefficients;
