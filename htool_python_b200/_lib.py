@@ -13,7 +13,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libhmb200.so"
 
 class hmb200_options(ctypes.Structure):
     _fields_ = [(n, c_int32) for n in ("stage_bytes", "stage_z_bytes", "n_stages", "consumer_warps", "piece1_bytes", "piece2_bytes",
-                                       "bin_rows", "unit_stages", "ctas", "build_transpose", "no_matmat", "stage_z_elems", "mm_stage_bytes", "mm_bin_cols")] + [("reserved", c_int32 * 2)]
+                                       "bin_rows", "unit_stages", "ctas", "build_transpose", "no_matmat", "stage_z_elems", "mm_stage_bytes", "mm_bin_cols", "mm_variant")] + [("reserved", c_int32 * 1)]
 
 
 class hmb200_info(ctypes.Structure):
@@ -21,7 +21,8 @@ class hmb200_info(ctypes.Structure):
                 ("n_leaves", c_int64), ("n_pieces1", c_int64), ("n_pieces2", c_int64), ("n_stages1", c_int64),
                 ("n_stages2", c_int64), ("n_reduce_segments", c_int64), ("stream1_bytes", c_int64), ("stream2_bytes", c_int64),
                 ("table_bytes", c_int64), ("workspace_bytes", c_int64), ("stored_coefficients", c_double),
-                ("pack_seconds", c_double), ("upload_seconds", c_double)]
+                ("pack_seconds", c_double), ("upload_seconds", c_double), ("mm_stream_bytes", c_int64), ("mm_tiles", c_int64),
+                ("mm_stages", c_int64), ("mm_rows", c_int64)]
 
 
 EXPORTS = {

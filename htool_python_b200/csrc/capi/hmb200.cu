@@ -16,7 +16,7 @@ using namespace hmb200;
 static thread_local std::string g_last_error;
 
 // ABI layout pinned (mirrored by htool_python_b200/_lib.py and checked in tests/test_capi_symbols.py)
-static_assert(sizeof(hmb200_flat) == 96 && sizeof(hmb200_options) == 64 && sizeof(hmb200_info) == 120, "hmb200 ABI layout changed");
+static_assert(sizeof(hmb200_flat) == 96 && sizeof(hmb200_options) == 64 && sizeof(hmb200_info) == 152, "hmb200 ABI layout changed");
 static_assert(sizeof(PacketHeader) == 16 && sizeof(PieceDesc) == 16 && sizeof(StageEntry) == 32 && sizeof(ZCopy) == 8 && sizeof(WorkUnit) == 8 && sizeof(ReduceSeg) == 16, "packet layout changed");
 
 #define CUDA_CHECK(expr)                                                                                               \
@@ -290,13 +290,14 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
         if (h->opt.build_matmat) {
             const int ldm = mm_max_ld(es);
             size_t m1 = mm_smem_bytes(1, es, h->opt.mm_stage_bytes, 0, 2, h->opt.mm_bin_cols, ldm), m2 = mm_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_elems, 2, 0, ldm);
-            if (es == 8) {
-                CUDA_CHECK(cudaFuncSetAttribute(hmatrix_mm_kernel<double, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m1));
-                CUDA_CHECK(cudaFuncSetAttribute(hmatrix_mm_kernel<double, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m2));
-            } else {
-                CUDA_CHECK(cudaFuncSetAttribute(hmatrix_mm_kernel<double2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m1));
-                CUDA_CHECK(cudaFuncSetAttribute(hmatrix_mm_kernel<double2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m2));
-            }
+            auto set2 = [&](auto k1a, auto k1b, auto k2a, auto k2b) {
+                CUDA_CHECK(cudaFuncSetAttribute(k1a, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m1));
+                CUDA_CHECK(cudaFuncSetAttribute(k1b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m1));
+                CUDA_CHECK(cudaFuncSetAttribute(k2a, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m2));
+                CUDA_CHECK(cudaFuncSetAttribute(k2b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m2));
+            };
+            if (es == 8) set2(hmatrix_mm_kernel<double, 1, true>, hmatrix_mm_kernel<double, 1, false>, hmatrix_mm_kernel<double, 2, true>, hmatrix_mm_kernel<double, 2, false>);
+            else set2(hmatrix_mm_kernel<double2, 1, true>, hmatrix_mm_kernel<double2, 1, false>, hmatrix_mm_kernel<double2, 2, true>, hmatrix_mm_kernel<double2, 2, false>);
         }
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
         // info
@@ -309,6 +310,7 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
         h->info.stream1_bytes = n.stream_bytes[0]; h->info.stream2_bytes = n.stream_bytes[1];
         h->info.table_bytes = n.table_bytes;
         h->info.workspace_bytes = (int64_t)h->xz_elems * es;
+        h->info.mm_stream_bytes = n.stream_bytes[2]; h->info.mm_tiles = n.n_pieces[2]; h->info.mm_stages = n.n_stages[2]; h->info.mm_rows = n.mm_rows;
     } catch (...) {
         hmb200_destroy(h);
         throw;
@@ -478,7 +480,7 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
             p.stream = po.stream[2]; p.stages = po.stages[2]; p.zcopies = po.zcopies[2]; p.units = po.units[2];
             p.n_units = po.n_units[2]; p.n_zcopies = 0; p.counter = h->counters; p.stage_bytes = o.mm_stage_bytes;
             size_t smem = mm_smem_bytes(1, h->es, o.mm_stage_bytes, 0, 2, o.mm_bin_cols, ld);
-            hmatrix_mm_kernel<T, 1><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[2]), threads, smem, h->stream>>>(p);
+            (o.mm_variant & 1 ? hmatrix_mm_kernel<T, 1, true> : hmatrix_mm_kernel<T, 1, false>)<<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[2]), threads, smem, h->stream>>>(p);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[1], h->stream));
@@ -492,7 +494,7 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
             p.stream = po.stream[1]; p.stages = po.stages[1]; p.zcopies = po.zcopies[1]; p.units = po.units[1];
             p.n_units = po.n_units[1]; p.n_zcopies = po.n_zcopies[1]; p.counter = h->counters + 1; p.stage_bytes = o.stage_bytes;
             size_t smem = mm_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_elems, 2, 0, ld);
-            hmatrix_mm_kernel<T, 2><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]), threads, smem, h->stream>>>(p);
+            (o.mm_variant & 2 ? hmatrix_mm_kernel<T, 2, true> : hmatrix_mm_kernel<T, 2, false>)<<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]), threads, smem, h->stream>>>(p);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[3], h->stream));

@@ -33,6 +33,7 @@ Options resolve_options(const hmb200_options *o) {
         if (o->stage_z_elems > 0) r.stage_z_elems = o->stage_z_elems;
         if (o->mm_stage_bytes > 0) r.mm_stage_bytes = o->mm_stage_bytes;
         if (o->mm_bin_cols > 0) r.mm_bin_cols = o->mm_bin_cols;
+        if (o->mm_variant > 0) r.mm_variant = o->mm_variant - 1;
     }
     r.stage_bytes   = (int)align_up((uint32_t)std::max(r.stage_bytes, 2048), 128);
     r.stage_z_bytes = (int)align_up((uint32_t)std::min(std::max(r.stage_z_bytes, 1024), 65536 - 128), 128);

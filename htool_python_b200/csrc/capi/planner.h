@@ -26,7 +26,8 @@ struct Options {
     int stage_z_elems   = 112;   // max operand elements (x / t entries) a phase-2 packet may reference: the multi-RHS kernel
                                  // stages stage_z_elems x (mu + pad) operand ROWS per packet
     int mm_stage_bytes  = 40960; // packet size of the multi-RHS phase-1 stream
-    int mm_bin_cols     = 128;   // columns of a source bin (the slice of X kept resident in shared memory)
+    int mm_bin_cols     = 128;
+    int mm_variant      = 1;     // bit 0 / bit 1: register-double-buffered DMMA fragments in multi-RHS phase 1 / phase 2   // columns of a source bin (the slice of X kept resident in shared memory)
 };
 Options resolve_options(const hmb200_options *opt);
 

@@ -55,6 +55,9 @@ __host__ __device__ inline size_t mm_smem_bytes(int phase, int elem_bytes, int s
     return 256 + x + (size_t)n_stages * (stage_bytes + z) + kMmSlack;
 }
 
+__device__ __forceinline__ void dmma884v(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
 __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
     asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
@@ -133,6 +136,48 @@ __device__ __forceinline__ void mm_tile(MmAcc<T, 2, NT> &acc, const T *A, int ld
     }
 }
 
+// the same contraction without the register double-buffering (fewer registers, no prologue): better for the short-K
+// tiles of phase 2 (K = rank)
+template <typename T, int NT>
+__device__ __forceinline__ void mm_tile_plain(MmAcc<T, 2, NT> &acc, const T *A, int lda, int nr, int r_base, const T *B, int ldb, int c_base, int nk, int lane) {
+    using S = Scalar<T>;
+    const int gid = lane >> 2, tig = lane & 3;
+    const int r0 = r_base + gid, r1 = r_base + 8 + gid;
+    const bool v0 = (unsigned)r0 < (unsigned)nr, v1 = (unsigned)r1 < (unsigned)nr;
+    const T *a0p = A + (v0 ? r0 : 0) + (size_t)tig * lda;
+    const T *a1p = A + (v1 ? r1 : 0) + (size_t)tig * lda;
+    const T *bp  = B + (size_t)tig * ldb + c_base + gid;
+    for (int k0 = 0; k0 < nk; k0 += 4) {
+        const bool kv = k0 + tig < nk;
+        const T a0 = (kv && v0) ? a0p[0] : S::zero(), a1 = (kv && v1) ? a1p[0] : S::zero();
+        T b[NT];
+#pragma unroll
+        for (int j = 0; j < NT; j++) b[j] = kv ? bp[8 * j] : S::zero();
+        if constexpr (sizeof(T) == 8) {
+#pragma unroll
+            for (int j = 0; j < NT; j++) {
+                dmma884v(acc.v[0][j][0][0], acc.v[0][j][0][1], a0, b[j]);
+                dmma884v(acc.v[1][j][0][0], acc.v[1][j][0][1], a1, b[j]);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < NT; j++) {
+                dmma884v(acc.v[0][j][0][0], acc.v[0][j][0][1], a0.x, b[j].x);
+                dmma884v(acc.v[0][j][1][0], acc.v[0][j][1][1], a0.x, b[j].y);
+                dmma884v(acc.v[1][j][0][0], acc.v[1][j][0][1], a1.x, b[j].x);
+                dmma884v(acc.v[1][j][1][0], acc.v[1][j][1][1], a1.x, b[j].y);
+                dmma884v(acc.v[0][j][0][0], acc.v[0][j][0][1], -a0.y, b[j].y);
+                dmma884v(acc.v[0][j][1][0], acc.v[0][j][1][1], a0.y, b[j].x);
+                dmma884v(acc.v[1][j][0][0], acc.v[1][j][0][1], -a1.y, b[j].y);
+                dmma884v(acc.v[1][j][1][0], acc.v[1][j][1][1], a1.y, b[j].x);
+            }
+        }
+        a0p += 4 * (size_t)lda;
+        a1p += 4 * (size_t)lda;
+        bp += 4 * (size_t)ldb;
+    }
+}
+
 template <typename T>
 __device__ __forceinline__ T mm_make(double re, double im);
 template <>
@@ -140,7 +185,7 @@ __device__ __forceinline__ double mm_make<double>(double re, double) { return re
 template <>
 __device__ __forceinline__ double2 mm_make<double2>(double re, double im) { return make_double2(re, im); }
 
-template <typename T, int PHASE>
+template <typename T, int PHASE, bool PIPE>
 __global__ void __launch_bounds__((kMmConsumerWarps + 1) * 32, 1) hmatrix_mm_kernel(const MmParams p) {
     constexpr int NW = kMmConsumerWarps;
     constexpr int NT = mm_ntiles_per_warp<T>();
@@ -262,7 +307,8 @@ __global__ void __launch_bounds__((kMmConsumerWarps + 1) * 32, 1) hmatrix_mm_ker
                     const uint4 d = *reinterpret_cast<const uint4 *>(pk + 16 + 16 * i);
                     const T *A    = reinterpret_cast<const T *>(pk + d.x);
                     const int nc = (int)(d.z >> 16), nr = (int)(d.w & 0xffu), ro = (int)((d.w >> 8) & 0xffu);
-                    mm_tile<T, NT>(acc, A, nr, nr, 16 * mg - ro, zarea + (size_t)(d.z & 0xffffu) * ld, ld, c_base, nc, lane);
+                    if (PIPE) mm_tile<T, NT>(acc, A, nr, nr, 16 * mg - ro, zarea + (size_t)(d.z & 0xffffu) * ld, ld, c_base, nc, lane);
+                    else mm_tile_plain<T, NT>(acc, A, nr, nr, 16 * mg - ro, zarea + (size_t)(d.z & 0xffffu) * ld, ld, c_base, nc, lane);
                 }
             }
             __syncwarp();
@@ -314,7 +360,8 @@ __global__ void __launch_bounds__((kMmConsumerWarps + 1) * 32, 1) hmatrix_mm_ker
                     const T *A = reinterpret_cast<const T *>(pk + d.x);
                     MmAcc<T, 2, NQ> a1;
                     a1.clear();
-                    mm_tile<T, NQ>(a1, A, lr, lr, 16 * mp, xres + (size_t)(d.z & 0xffffu) * ld, ld, cb, nq, lane);
+                    if (PIPE) mm_tile<T, NQ>(a1, A, lr, lr, 16 * mp, xres + (size_t)(d.z & 0xffffu) * ld, ld, cb, nq, lane);
+                    else mm_tile_plain<T, NQ>(a1, A, lr, lr, 16 * mp, xres + (size_t)(d.z & 0xffffu) * ld, ld, cb, nq, lane);
 #pragma unroll
                     for (int mt = 0; mt < 2; mt++) {
                         const int r = 16 * mp + 8 * mt + gid;
@@ -357,16 +404,38 @@ __global__ void __launch_bounds__(256) reduce_rows_kernel(const ReduceSeg *segs,
     for (uint32_t sidx = wid; sidx < n_segs; sidx += nw) {
         const uint4 sg = __ldg(reinterpret_cast<const uint4 *>(segs + sidx));
         const int total = (int)sg.w * cpr;
-        for (int e = lane; e < total; e += 32) {
-            const int l = e / cpr, c = (e - l * cpr) * V;
-            double2 s = make_double2(0.0, 0.0);
-            for (uint32_t q = 0; q < sg.z; q++) {
-                const uint32_t row = __ldg(part_rows + sg.y + q) + l;
-                const double2 v    = *reinterpret_cast<const double2 *>(ws + (size_t)row * ld + c);
-                s.x += v.x;
-                s.y += v.y;
+        T *dst_base = ws + (size_t)sg.x * ld;
+        for (uint32_t q0 = 0; q0 < sg.z; q0 += 32) { // part rows: 32 at a time in registers, handed out by shuffles
+            const uint32_t nq = min(32u, sg.z - q0);
+            const uint32_t my_row = (uint32_t)lane < nq ? __ldg(part_rows + sg.y + q0 + lane) : 0u;
+            for (int e = lane; e < ((total + 31) & ~31); e += 32) {
+                const bool act = e < total;
+                const int l = act ? e / cpr : 0, c = act ? (e - l * cpr) * V : 0;
+                double2 s = make_double2(0.0, 0.0);
+                if (q0 > 0 && act) s = *reinterpret_cast<const double2 *>(dst_base + (size_t)l * ld + c);
+                uint32_t q = 0;
+                for (; q + 4 <= nq; q += 4) {
+                    const uint32_t r0 = __shfl_sync(0xffffffffu, my_row, q), r1 = __shfl_sync(0xffffffffu, my_row, q + 1);
+                    const uint32_t r2 = __shfl_sync(0xffffffffu, my_row, q + 2), r3 = __shfl_sync(0xffffffffu, my_row, q + 3);
+                    if (act) {
+                        const double2 v0 = *reinterpret_cast<const double2 *>(ws + (size_t)(r0 + l) * ld + c);
+                        const double2 v1 = *reinterpret_cast<const double2 *>(ws + (size_t)(r1 + l) * ld + c);
+                        const double2 v2 = *reinterpret_cast<const double2 *>(ws + (size_t)(r2 + l) * ld + c);
+                        const double2 v3 = *reinterpret_cast<const double2 *>(ws + (size_t)(r3 + l) * ld + c);
+                        s.x = (((s.x + v0.x) + v1.x) + v2.x) + v3.x;
+                        s.y = (((s.y + v0.y) + v1.y) + v2.y) + v3.y;
+                    }
+                }
+                for (; q < nq; q++) {
+                    const uint32_t r0 = __shfl_sync(0xffffffffu, my_row, q);
+                    if (act) {
+                        const double2 v0 = *reinterpret_cast<const double2 *>(ws + (size_t)(r0 + l) * ld + c);
+                        s.x += v0.x;
+                        s.y += v0.y;
+                    }
+                }
+                if (act) *reinterpret_cast<double2 *>(dst_base + (size_t)l * ld + c) = s;
             }
-            *reinterpret_cast<double2 *>(ws + (size_t)(sg.x + l) * ld + c) = s;
         }
     }
 }

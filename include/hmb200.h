@@ -72,7 +72,8 @@ typedef struct hmb200_options {
                                 stages that many operand ROWS of (mu + pad) per packet */
     int32_t mm_stage_bytes;  /* packet bytes of the multi-RHS phase-1 stream (default 40960) */
     int32_t mm_bin_cols;     /* entries of x per source bin, resident in shared memory in multi-RHS phase 1 (default 128) */
-    int32_t reserved[2];
+    int32_t mm_variant;      /* tuning: 1 + bitmask (bit 0 / 1: double-buffered DMMA fragments in multi-RHS phase 1 / 2); 0 = default */
+    int32_t reserved[1];
 } hmb200_options;
 
 typedef struct hmb200_handle hmb200_handle;
@@ -89,6 +90,7 @@ typedef struct hmb200_info {
     double stored_coefficients;           /* W = sum r(m+n) + sum m n, mirrored leaves counted once,
                                              symmetric dense leaves m(n+1)/2 (core/hmatrix/hmatrix_output.hpp:153-208) */
     double pack_seconds, upload_seconds;
+    int64_t mm_stream_bytes, mm_tiles, mm_stages, mm_rows; /* multi-RHS phase-1 stream; workspace rows of the multi-RHS path */
 } hmb200_info;
 
 /* ---- life cycle ------------------------------------------------------------------------------------------------

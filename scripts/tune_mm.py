@@ -18,6 +18,7 @@ for cfg in sys.argv[3:] or [""]:
     opts = {k: int(v) for k, v in (kv.split("=") for kv in cfg.split(",") if kv)}
     e = Engine(flat, **opts)
     inf = e.info
+    print('   mm info:', {k: inf[k] for k in ('mm_stream_bytes','mm_tiles','mm_stages','mm_rows','n_pieces2','n_stages2','workspace_bytes')}, 'sum_r rows', int(np.maximum(flat.rank,0).sum()))
     for _ in range(2): e.add_matrix_product_row_major("N", 1.0, X, 0.0, Y, mu)
     torch.cuda.synchronize(); e.enable_timing(True)
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)

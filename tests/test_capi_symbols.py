@@ -33,7 +33,7 @@ def test_struct_layouts_match_header():
 
     assert ctypes.sizeof(hmb200_flat) == 96
     assert ctypes.sizeof(_lib.hmb200_options) == 64
-    assert ctypes.sizeof(_lib.hmb200_info) == 120
+    assert ctypes.sizeof(_lib.hmb200_info) == 152
 
 
 def test_no_cpu_fallback_without_gpu():
