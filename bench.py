@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--kernel", default="laplace", choices=["laplace", "helmholtz"],
                     help="laplace = BASELINE.json configs[1] (the metric); helmholtz = configs[2] (complex<double>, off-metric check)")
     ap.add_argument("--wavenumber", type=float, default=0.0, help="helmholtz: k (default: 10 points per wavelength)")
+    ap.add_argument("--rhs", type=int, default=1, help="right-hand sides per step (64 = BASELINE.json configs[3], DMMA multi-RHS path; off-metric)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--engine-opts", default="", help="k=v,k=v overrides of hmb200_options (tuning runs)")
     return ap.parse_args()
@@ -193,15 +194,28 @@ def run_b200(args):
         x_user = x_user + 1j * rng.random(n)
     tdt = torch.complex128 if flat.dtype == "z" else torch.float64
     perm_s = flat.source_permutation
-    x_cluster = torch.from_numpy(np.ascontiguousarray(x_user[perm_s])).to(dev)
-    y_cluster = torch.zeros(n, dtype=tdt, device=dev)
+    mu = max(1, args.rhs)
+    if mu > 1:  # X: n x mu, Fortran-ordered for the user API, row-major in cluster numbering for the operator interface
+        x_user = np.asfortranarray(np.stack([np.roll(x_user, 7 * j) * (1.0 + 0.01 * j) for j in range(mu)], axis=1))
+        x_cluster = torch.from_numpy(np.ascontiguousarray(x_user[perm_s])).to(dev)
+        y_cluster = torch.zeros(n, mu, dtype=tdt, device=dev)
+    else:
+        x_cluster = torch.from_numpy(np.ascontiguousarray(x_user[perm_s])).to(dev)
+        y_cluster = torch.zeros(n, dtype=tdt, device=dev)
 
-    if world > 1:
+    if mu > 1 and world > 1:
+        def step():
+            op.matmat_cluster_(x_cluster.view(-1), y_cluster, mu)
+    elif mu > 1:
+        def step():
+            engine.add_matrix_product_row_major("N", 1.0, x_cluster, 0.0, y_cluster, mu)
+    elif world > 1:
         def step():
             op.matvec_cluster_(x_cluster, y_cluster)
     else:
         def step():
             engine.add_vector_product("N", 1.0, x_cluster, 0.0, y_cluster)
+    apply_user = (lambda: op @ x_user) if mu > 1 else (lambda: op * x_user)
 
     # ---- device-resident timed region ------------------------------------------------------------------------
     for _ in range(args.warmup):
@@ -229,11 +243,11 @@ def run_b200(args):
 
     # ---- end to end through the public API with host buffers ----------------------------------------------------
     for _ in range(2):
-        y_user = op * x_user
+        y_user = apply_user()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        y_user = op * x_user
+        y_user = apply_user()
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -258,6 +272,14 @@ def run_b200(args):
                 "frac": round(achieved / peak, 4), "traffic": None, "algorithmic_bytes_per_launch": alg[dom],
                 "kernel_ms": {k: round(v, 4) for k, v in kms.items()},
                 "whole_product_GBps": round(flat.algorithmic_bytes(1) / (kms["total"] * 1e-3) / 1e9, 1) if kms["total"] > 0 else None}
+    if mu > 1:  # multi-RHS: bounded by the FP64 tensor (DMMA) pipe; kernel_ms are per pass of 64 (32 complex) columns
+        passes = -(-mu // (64 if es == 8 else 32))
+        flops = (2 if es == 8 else 8) * mu * flat.stored_coefficients
+        tf = flops / (kms["total"] * passes * 1e-3) / 1e12 if kms["total"] > 0 else 0.0
+        roofline = {"bound": "tensor", "kernel": "hmatrix_mm_kernel<T,1|2> (mma.sync.m8n8k4.f64)", "achieved": round(tf, 2), "peak": 37.0,
+                    "peak_source": "measured DMMA issue rate on this B200 (profiles/r01_dmma_rate.log); MEASURED_PEAKS.json has no FP64 figure",
+                    "unit": "TFLOP/s", "frac": round(tf / 37.0, 4), "traffic": None, "algorithmic_flops_per_step": flops, "passes": passes,
+                    "kernel_ms_per_pass": {k: round(v, 4) for k, v in kms.items()}}
 
     # ---- CPU baseline + parity (rank 0, N=1 only) ---------------------------------------------------------------------
     cpu = None
@@ -269,16 +291,16 @@ def run_b200(args):
 
     if rank == 0:
         line = {
-            "metric": METRIC, "value": round(1e3 / ms_step, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "metric": METRIC, "value": round(mu * 1e3 / ms_step, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if flat.dtype == "d" else "c128",
             "data": "synthetic",
             "config": {"workload": f"{WORKLOADS[args.kernel]} H-matrix, N={n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
-                                   f"leaf {args.leaf}, single-RHS matvec (BASELINE.json configs[{1 if args.kernel == 'laplace' else 2}])",
-                       "partition": f"block-row slabs x{world}", "l2": "inputs larger than L2 (factor stream >> 126 MB, read once per step)",
+                                   f"leaf {args.leaf}, {'single-RHS matvec' if mu == 1 else str(mu) + '-RHS matmat (DMMA path)'} (BASELINE.json configs[{(1 if mu == 1 else 3) if args.kernel == 'laplace' else 2}])",
+                       "rhs_per_step": mu, "partition": f"block-row slabs x{world}", "l2": "inputs larger than L2 (factor stream >> 126 MB, read once per step)",
                        "stored_coefficients_rank0": flat.stored_coefficients, "leaves_rank0": flat.n_leaves,
                        "assembly": "reference HMatrixTreeBuilder (OpenMP, native generator), outside the timed region", **build_t},
             "clocks": clocks,
-            "e2e": {"value": round(1.0 / e2e_step, 3), "unit": UNIT, "h2d_bytes_per_step": es * n, "d2h_bytes_per_step": es * n,
+            "e2e": {"value": round(mu / e2e_step, 3), "unit": UNIT, "h2d_bytes_per_step": es * n * mu, "d2h_bytes_per_step": es * n * mu,
                     "ms_per_step": round(e2e_step * 1e3, 4)},
             "gpu_launches": int(launches),
             "roofline": roofline,
@@ -298,7 +320,9 @@ def cpu_reference_product(H, flat, x_user, threads, budget_s, log):
 
     ro = helpers_ref.ref_ops()
     ro.omp_set_num_threads(threads)
-    fn = getattr(ro, "vector_product_user_addr_" + flat.dtype)
+    mu = x_user.shape[1] if x_user.ndim == 2 else 1
+    # multi-RHS: add_hmatrix_matrix_product(exec_compat::par, ...) on the Fortran-ordered block (hmatrix.hpp:119-138 path)
+    fn = getattr(ro, ("matrix_product_user_addr_" if mu > 1 else "vector_product_user_addr_") + flat.dtype)
     y = fn(H.address, x_user, True)  # warm-up
     times = []
     t_all = time.perf_counter()
@@ -308,10 +332,10 @@ def cpu_reference_product(H, flat, x_user, threads, budget_s, log):
         times.append(time.perf_counter() - t0)
     best = min(times)
     log(f"cpu reference product: {len(times)} runs, best {best * 1e3:.1f} ms, {threads} threads")
-    return {"value": round(1.0 / best, 4), "unit": UNIT, "cores": threads, "kind": "reference",
-            "sample": f"{len(times)} full matvecs of the same N={flat.n_cols} operator (best), reference OpenMP path "
-                      "add_hmatrix_vector_product(exec_compat::par) compiled from the reference sources (oracle/_ref)",
-            "ms_per_matvec": round(best * 1e3, 2)}, y
+    return {"value": round(mu / best, 4), "unit": UNIT, "cores": threads, "kind": "reference",
+            "sample": f"{len(times)} full products ({mu} RHS each) of the same N={flat.n_cols} operator (best), reference OpenMP path "
+                      "add_hmatrix_{vector,matrix}_product(exec_compat::par) compiled from the reference sources (oracle/_ref)",
+            "ms_per_product": round(best * 1e3, 2)}, y
 
 
 def run_reference(args):
@@ -331,14 +355,19 @@ def run_reference(args):
     ro.omp_set_num_threads(thr)
     tree, H, flat, build_t = assemble(args, 1, 0, log)
     x_user = np.random.default_rng(1).random(args.n)
-    fn = getattr(ro, "vector_product_user_addr_" + flat.dtype)
+    if flat.dtype == "z":
+        x_user = x_user + 1j * np.random.default_rng(2).random(args.n)
+    mu = max(1, args.rhs)
+    if mu > 1:
+        x_user = np.asfortranarray(np.stack([np.roll(x_user, 7 * j) * (1.0 + 0.01 * j) for j in range(mu)], axis=1))
+    fn = getattr(ro, ("matrix_product_user_addr_" if mu > 1 else "vector_product_user_addr_") + flat.dtype)
     for _ in range(max(1, min(args.warmup, 3))):
         fn(H.address, x_user, True)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         fn(H.address, x_user, True)
     dt = (time.perf_counter() - t0) / args.steps
-    v = round(1.0 / dt, 4)
+    v = round(max(1, args.rhs) / dt, 4)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(dt * 1e3, 3), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"Laplace 1/(4 pi r) H-matrix, N={args.n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
