@@ -281,6 +281,14 @@ def run_b200(args):
                     "unit": "TFLOP/s", "frac": round(tf / 37.0, 4), "traffic": None, "algorithmic_flops_per_step": flops, "passes": passes,
                     "kernel_ms_per_pass": {k: round(v, 4) for k, v in kms.items()}}
 
+    try:  # traffic of the dominant kernel from the committed ncu capture of this exact workload (null otherwise)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(f"{args.kernel}_{n}_{world}" + (f"_rhs{mu}" if mu > 1 else ""))
+        if tr and args.eps == 1e-3 and args.eta == 10.0 and args.leaf == 64:
+            roofline["traffic"] = tr["phase2" if (mu > 1 or dom == "phase2") else "phase1"]
+            roofline["traffic_source"] = tr["source"]
+    except Exception:
+        pass
+
     # ---- CPU baseline + parity (rank 0, N=1 only) ---------------------------------------------------------------------
     cpu = None
     parity = None
