@@ -35,6 +35,9 @@ EXPORTS = {
     "hmb200_add_vector_product_z": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int]),
     "hmb200_add_matrix_product_row_major_d": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int]),
     "hmb200_add_matrix_product_row_major_z": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int]),
+    "hmb200_set_cluster_offsets": (c_int, [c_void_p, c_int, c_int]),
+    "hmb200_add_sub_matrix_product_to_local_d": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int]),
+    "hmb200_add_sub_matrix_product_to_local_z": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int]),
     "hmb200_permute_gather": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "hmb200_permute_scatter": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "hmb200_set_permutations": (c_int, [c_void_p, c_void_p, c_void_p]),

@@ -74,6 +74,9 @@ struct hmb200_handle {
     uint64_t ws_mm_elems = 0;
     void *xbuf = nullptr; // device staging for multi-RHS inputs
     uint64_t xbuf_elems = 0;
+    void *xsub = nullptr; // zero-extended source window of add_sub_matrix_product_to_local
+    uint64_t xsub_elems = 0;
+    int target_offset = 0, source_offset = 0; // offsets of the root block in the target / source tree numbering
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
     uint32_t *counters = nullptr; // [2]
@@ -114,6 +117,19 @@ void staged_copy(void *dst, const void *src, size_t bytes) {
         const size_t o = (size_t)i * kChunk;
         std::memcpy((uint8_t *)dst + o, (const uint8_t *)src + o, std::min(kChunk, bytes - o));
     }
+}
+
+// a caller buffer that is already page-locked (cudaHostAlloc / cudaHostRegister / torch pin_memory) is DMA'd directly
+bool host_is_pinned(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+// host source of an H2D copy: the caller's buffer itself when page-locked, else the pinned slot after a staging copy
+const void *stage_in(const void *user, void *slot, size_t bytes) {
+    if (host_is_pinned(user)) return user;
+    staged_copy(slot, user, bytes);
+    return slot;
 }
 
 void ensure_pinned(hmb200_handle *h, size_t bytes) {
@@ -424,16 +440,16 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
         ensure_pinned(h, in_b + out_b + 64);
         ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out, h->es);
         uint8_t *pin = (uint8_t *)h->pinned, *pout = pin + ((in_b + 63) & ~(size_t)63);
-        staged_copy(pin, in, in_b);
-        CUDA_CHECK(cudaMemcpyAsync(h->xz, pin, in_b, cudaMemcpyHostToDevice, h->stream));
+        CUDA_CHECK(cudaMemcpyAsync(h->xz, stage_in(in, pin, in_b), in_b, cudaMemcpyHostToDevice, h->stream));
+        void *hout = host_is_pinned(out) ? out : (void *)pout;
         if (!beta_zero) {
-            staged_copy(pout, out, out_b);
-            CUDA_CHECK(cudaMemcpyAsync(h->ybuf, pout, out_b, cudaMemcpyHostToDevice, h->stream));
+            if (hout != out) staged_copy(pout, out, out_b);
+            CUDA_CHECK(cudaMemcpyAsync(h->ybuf, hout, out_b, cudaMemcpyHostToDevice, h->stream));
         }
         run_product<T>(h, po, alpha, beta, h->ybuf, nullptr);
-        CUDA_CHECK(cudaMemcpyAsync(pout, h->ybuf, out_b, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_CHECK(cudaMemcpyAsync(hout, h->ybuf, out_b, cudaMemcpyDeviceToHost, h->stream));
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
-        staged_copy(out, pout, out_b);
+        if (hout != out) staged_copy(out, pout, out_b);
     }
     return 0;
 }
@@ -521,11 +537,11 @@ int matrix_product(hmb200_handle *h, char trans, const double *alpha, const void
         ensure_dev(&h->xbuf, &h->xbuf_elems, (uint64_t)po.n_in * mu, h->es);
         uint8_t *pin = (uint8_t *)h->pinned;
         pout         = pin + ((in_b + 63) & ~(size_t)63);
-        staged_copy(pin, in, in_b);
-        CUDA_CHECK(cudaMemcpyAsync(h->xbuf, pin, in_b, cudaMemcpyHostToDevice, h->stream));
+        CUDA_CHECK(cudaMemcpyAsync(h->xbuf, stage_in(in, pin, in_b), in_b, cudaMemcpyHostToDevice, h->stream));
         dout = (T *)h->ybuf + po.n_out; // [column scratch | row-major block]
+        if (host_is_pinned(out)) pout = (uint8_t *)out;
         if (!beta_zero) {
-            staged_copy(pout, out, out_b);
+            if ((void *)pout != out) staged_copy(pout, out, out_b);
             CUDA_CHECK(cudaMemcpyAsync(dout, pout, out_b, cudaMemcpyHostToDevice, h->stream));
         }
         din = (const T *)h->xbuf;
@@ -548,8 +564,45 @@ int matrix_product(hmb200_handle *h, char trans, const double *alpha, const void
     if (mem == HMB200_HOST) {
         CUDA_CHECK(cudaMemcpyAsync(pout, dout, out_b, cudaMemcpyDeviceToHost, h->stream));
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
-        staged_copy(out, pout, out_b);
+        if ((void *)pout != out) staged_copy(out, pout, out_b);
     }
+    return 0;
+}
+
+// out += A[:, offset:offset+size] * in (row-major size x mu window of the source, `offset` in source-tree numbering):
+// clip to the operator's source range and extend by zero, as the reference does on the host
+// (core/distributed_operator/implementations/local_to_local_operators/hmatrix.hpp:34-51)
+template <typename T>
+int sub_matrix_product(hmb200_handle *h, const void *in, void *out, int mu, int offset, int size, int mem) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    if (mu <= 0) throw std::runtime_error("mu must be positive");
+    if (size < 0) throw std::runtime_error("negative window size");
+    PackedOp &po = h->ops[0];
+    const int src_off = h->source_offset, src_end = src_off + po.n_in;
+    const int w0 = std::max(offset, src_off), w1 = std::min(src_end, offset + size);
+    if (w1 - w0 <= 0) return 0; // empty intersection: out is left untouched (beta = 1)
+    const double one[2] = {1.0, 0.0};
+    const size_t win_b = (size_t)(w1 - w0) * mu * sizeof(T), out_b = (size_t)po.n_out * mu * sizeof(T);
+    const T *win = (const T *)in + (size_t)(w0 - offset) * mu;
+    ensure_dev(&h->xsub, &h->xsub_elems, (uint64_t)po.n_in * mu, h->es);
+    T *xs = (T *)h->xsub;
+    const bool whole = (w0 == src_off && w1 == src_end);
+    if (!whole) CUDA_CHECK(cudaMemsetAsync(xs, 0, (size_t)po.n_in * mu * sizeof(T), h->stream));
+    if (mem == HMB200_DEVICE) {
+        CUDA_CHECK(cudaMemcpyAsync(xs + (size_t)(w0 - src_off) * mu, win, win_b, cudaMemcpyDeviceToDevice, h->stream));
+        return matrix_product<T>(h, 'N', one, xs, one, out, mu, HMB200_DEVICE);
+    }
+    ensure_pinned(h, win_b + out_b + 64);
+    ensure_dev(&h->ybuf2, &h->ybuf2_elems, (uint64_t)po.n_out * mu, h->es);
+    uint8_t *pin = (uint8_t *)h->pinned, *pout = pin + ((win_b + 63) & ~(size_t)63);
+    CUDA_CHECK(cudaMemcpyAsync(xs + (size_t)(w0 - src_off) * mu, stage_in(win, pin, win_b), win_b, cudaMemcpyHostToDevice, h->stream));
+    void *hout = host_is_pinned(out) ? out : (void *)pout;
+    if (hout != out) staged_copy(pout, out, out_b);
+    CUDA_CHECK(cudaMemcpyAsync(h->ybuf2, hout, out_b, cudaMemcpyHostToDevice, h->stream));
+    matrix_product<T>(h, 'N', one, xs, one, h->ybuf2, mu, HMB200_DEVICE);
+    CUDA_CHECK(cudaMemcpyAsync(hout, h->ybuf2, out_b, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_CHECK(cudaStreamSynchronize(h->stream));
+    if (hout != out) staged_copy(out, pout, out_b);
     return 0;
 }
 
@@ -571,8 +624,8 @@ int matvec_user(hmb200_handle *h, const void *x, void *y, int mem, int mu) {
         ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out * mu, h->es);
         uint8_t *pin = (uint8_t *)h->pinned;
         pout         = pin + ((in_b + 63) & ~(size_t)63);
-        staged_copy(pin, x, in_b);
-        CUDA_CHECK(cudaMemcpyAsync(h->xbuf, pin, in_b, cudaMemcpyHostToDevice, h->stream));
+        CUDA_CHECK(cudaMemcpyAsync(h->xbuf, stage_in(x, pin, in_b), in_b, cudaMemcpyHostToDevice, h->stream));
+        if (host_is_pinned(y)) pout = (uint8_t *)y;
         dx = (const T *)h->xbuf;
         dy = (T *)h->ybuf;
     }
@@ -596,7 +649,7 @@ int matvec_user(hmb200_handle *h, const void *x, void *y, int mem, int mu) {
     if (mem == HMB200_HOST) {
         CUDA_CHECK(cudaMemcpyAsync(pout, dy, out_b, cudaMemcpyDeviceToHost, h->stream));
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
-        staged_copy(y, pout, out_b);
+        if ((void *)pout != y) staged_copy(y, pout, out_b);
     }
     return 0;
 }
@@ -643,6 +696,7 @@ void hmb200_destroy(hmb200_handle *h) {
     cudaFree(h->xz);
     cudaFree(h->ybuf);
     cudaFree(h->xbuf);
+    cudaFree(h->xsub);
     cudaFree(h->ws_mm);
     cudaFree(h->ybuf2);
     cudaFree(h->counters);
@@ -677,6 +731,18 @@ int hmb200_add_matrix_product_row_major_d(hmb200_handle *h, char trans, const do
 }
 int hmb200_add_matrix_product_row_major_z(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mu, int mem) {
     return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return matrix_product<double2>(h, trans, alpha, in, beta, out, mu, mem); });
+}
+int hmb200_set_cluster_offsets(hmb200_handle *h, int target_offset, int source_offset) {
+    if (!h) { g_last_error = "null handle"; return 1; }
+    h->target_offset = target_offset;
+    h->source_offset = source_offset;
+    return 0;
+}
+int hmb200_add_sub_matrix_product_to_local_d(hmb200_handle *h, const double *in, double *out, int mu, int offset, int size, int mem) {
+    return guarded([&] { if (!h || h->es != 8) throw std::runtime_error("handle is not a real (double) engine"); return sub_matrix_product<double>(h, in, out, mu, offset, size, mem); });
+}
+int hmb200_add_sub_matrix_product_to_local_z(hmb200_handle *h, const double *in, double *out, int mu, int offset, int size, int mem) {
+    return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return sub_matrix_product<double2>(h, in, out, mu, offset, size, mem); });
 }
 
 static int permute_impl(bool gather, const int32_t *perm, int off, int n, const void *in, void *out, int elem_bytes, int mu, int mem, void *stream) {

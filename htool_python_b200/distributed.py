@@ -113,6 +113,18 @@ class B200DistributedOperator:
         self.engine.add_matrix_product_row_major("N", 1.0, X_cluster, 0.0, Y_cluster.view(-1)[o * mu:(o + s) * mu], mu)
         return allgather_slabs_(Y_cluster, self.offs, self.sizes, mu, self.group)
 
+    def internal_sub_vector_product_global_to_local(self, x, offset: int):
+        """y_local = A_p[:, offset:offset+len(x)] x : the window product GenEO's coarse-space assembly uses
+        (src/htool/distributed_operator/distributed_operator.hpp:67-78 ->
+        internal_add_distributed_operator_vector_sub_product_global_to_local); x in source CLUSTER numbering, host array;
+        returns this rank's slab (length local target size) like the reference."""
+        x = np.ascontiguousarray(x, dtype=self.np_dtype)
+        if x.ndim != 1:
+            raise RuntimeError("Wrong dimension for DistributedOperator-vector product")
+        out = np.zeros(self.sizes[self.rank], dtype=self.np_dtype)
+        self.engine.add_sub_matrix_product_to_local(x, out, 1, int(offset), x.shape[0])
+        return out
+
     # ---- user-numbering products on host arrays (what the reference's Python API does) ------------------------
     def _permute(self, gather: bool, perm, n, src, dst, mu):
         import torch

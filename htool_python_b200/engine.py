@@ -53,6 +53,8 @@ class Engine:
         if not h:
             raise RuntimeError("hmb200_create failed: " + _lib.last_error())
         self._h = ctypes.c_void_p(h)
+        self.target_offset, self.source_offset = int(flat.target_offset or 0), int(flat.source_offset or 0)
+        _lib.check(lib.hmb200_set_cluster_offsets(self._h, self.target_offset, self.source_offset))
         self._has_perms = False
         # user-numbering products need the root block of both trees (a row slab's slots map to arbitrary user indices)
         if (flat.target_permutation is not None and len(flat.target_permutation) == flat.n_rows and flat.target_offset == 0
@@ -148,6 +150,19 @@ class Engine:
             raise ValueError("in and out must both be host arrays or both CUDA tensors")
         fn = _lib.lib().hmb200_add_matrix_product_row_major_z if self.is_complex else _lib.lib().hmb200_add_matrix_product_row_major_d
         _lib.check(fn(self._h, trans.encode(), _scalar(alpha, self.is_complex), px, _scalar(beta, self.is_complex), po, int(mu), mx))
+        return out
+
+    def add_sub_matrix_product_to_local(self, x, out, mu: int, offset: int, size: int):
+        """out += A[:, offset:offset+size] * x, IN PLACE; x = (size x mu) row-major window of the source in source-tree
+        numbering (virtual_global_to_local_operator.hpp:33; restricted_operator.hpp:173-194)."""
+        if size < 0 or mu <= 0:
+            raise ValueError("size must be >= 0 and mu > 0")
+        px, mx = self._ptr(x, size * mu, False) if size else (0, None)
+        po, mo = self._ptr(out, self.shape[0] * mu, True)
+        if size and mx != mo:
+            raise ValueError("in and out must both be host arrays or both CUDA tensors")
+        fn = _lib.lib().hmb200_add_sub_matrix_product_to_local_z if self.is_complex else _lib.lib().hmb200_add_sub_matrix_product_to_local_d
+        _lib.check(fn(self._h, px, po, int(mu), int(offset), int(size), mo))
         return out
 
     def matvec_user(self, x, out=None):

@@ -116,6 +116,16 @@ int hmb200_add_vector_product_z(hmb200_handle *h, char trans, const double *alph
 int hmb200_add_matrix_product_row_major_d(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mu, int mem);
 int hmb200_add_matrix_product_row_major_z(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mu, int mem);
 
+/* Replaces VirtualGlobalToLocalOperator::add_sub_matrix_product_to_local (same header :33) as implemented by
+ *   RestrictedGlobalToLocalOperator / LocalToLocalHMatrix (core/distributed_operator/implementations/global_to_local_operators/
+ *   restricted_operator.hpp:173-194, .../local_to_local_operators/hmatrix.hpp:34-51): out += A[:, offset:offset+size] * in,
+ *   `in` = size x mu row-major rows of the source window, `offset` in the numbering of the source tree (the operator's own
+ *   source cluster starts at the source offset given to hmb200_set_cluster_offsets, default 0).  The window is clipped to
+ *   the operator's source range exactly like the reference and extended by zero on the device. */
+int hmb200_set_cluster_offsets(hmb200_handle *h, int target_offset, int source_offset);
+int hmb200_add_sub_matrix_product_to_local_d(hmb200_handle *h, const double *in, double *out, int mu, int offset, int size, int mem);
+int hmb200_add_sub_matrix_product_to_local_z(hmb200_handle *h, const double *in, double *out, int mu, int offset, int size, int mem);
+
 /* ---- permutations (bit-exact) -----------------------------------------------------------------------------------
  * gather : out[i] = in[perm[off+i]-off]   user_to_cluster / global_to_root_cluster (core/clustering/cluster_node.hpp:110-119,162-175)
  * scatter: out[perm[off+i]-off] = in[i]   cluster_to_user / root_cluster_to_global (core/clustering/cluster_node.hpp:99-109,149-161)

@@ -316,3 +316,68 @@ def test_multi_rhs_dmma(name, mu):
     assert Yu.flags.f_contiguous and rel_err(Yu, Yu2) < TOL
     e.close()
     e2.close()
+
+
+@pytest.mark.parametrize("dtype", ["d", "z"])
+@pytest.mark.parametrize("mu", [1, 5])
+def test_add_sub_matrix_product_to_local(dtype, mu):
+    """out += A[:, offset:offset+size] * in with the reference's clipping rules
+    (restricted_operator.hpp:173-194, local_to_local_operators/hmatrix.hpp:34-51): oracle = the zero-extended product."""
+    rng = np.random.default_rng(31 + mu)
+    m, n, src_off = 210, 170, 1000
+    flat = synthetic_flat(rng, m, n, dtype=dtype, max_leaf=48)
+    flat.source_offset = src_off
+    e = _engine(flat)
+    for offset, size in [(src_off, n), (src_off + 17, 40), (src_off - 30, 60), (src_off + n - 10, 50), (src_off - 5, n + 10),
+                         (src_off + 40, 0), (0, 100), (src_off + n, 10)]:
+        X = np.ascontiguousarray(helpers.rand_vec(rng, max(size, 1), flat.np_dtype, mu))[:size]
+        Y0 = np.ascontiguousarray(helpers.rand_vec(rng, m, flat.np_dtype, mu))
+        ext = np.zeros((n, mu), dtype=flat.np_dtype)
+        w0, w1 = max(offset, src_off), min(src_off + n, offset + size)
+        if w1 > w0:
+            ext[w0 - src_off:w1 - src_off] = X.reshape(size, mu)[w0 - offset:w1 - offset]
+        Y_ref = Y0.copy()
+        fo.add_matrix_product_row_major(flat, "N", 1.0, ext, 1.0, Y_ref, mu)
+        Y = Y0.copy()
+        e.add_sub_matrix_product_to_local(np.ascontiguousarray(X), Y, mu, offset, size)
+        assert rel_err(Y, Y_ref) < TOL, (offset, size)
+        if w1 <= w0:
+            assert np.array_equal(Y, Y0)
+    # device pointers
+    import torch
+
+    offset, size = src_off + 20, 64
+    X = np.ascontiguousarray(helpers.rand_vec(rng, size, flat.np_dtype, mu))
+    Y0 = np.ascontiguousarray(helpers.rand_vec(rng, m, flat.np_dtype, mu))
+    ext = np.zeros((n, mu), dtype=flat.np_dtype)
+    ext[20:20 + size] = X.reshape(size, mu)
+    Y_ref = Y0.copy()
+    fo.add_matrix_product_row_major(flat, "N", 1.0, ext, 1.0, Y_ref, mu)
+    Xd, Yd = torch.from_numpy(X).cuda().reshape(-1), torch.from_numpy(Y0.copy()).cuda().reshape(-1)
+    e.add_sub_matrix_product_to_local(Xd, Yd, mu, offset, size)
+    assert rel_err(Yd.cpu().numpy().reshape(Y_ref.shape), Y_ref) < TOL
+    e.close()
+
+
+def test_page_locked_host_buffers_skip_staging():
+    """HOST entry points DMA straight from / into page-locked caller buffers; results identical to pageable buffers."""
+    import torch
+
+    rng = np.random.default_rng(77)
+    flat = synthetic_flat(rng, 300, 260, max_leaf=64)
+    e = _engine(flat)
+    x = helpers.rand_vec(rng, 260, np.float64)
+    y0 = helpers.rand_vec(rng, 300, np.float64)
+    y_page = y0.copy()
+    e.add_vector_product("N", 1.5, x, -0.5, y_page)
+    xp = torch.from_numpy(x.copy()).pin_memory()
+    yp = torch.from_numpy(y0.copy()).pin_memory()
+    e.add_vector_product("N", 1.5, xp.numpy(), -0.5, yp.numpy())
+    assert np.array_equal(yp.numpy(), y_page)
+    X = np.ascontiguousarray(helpers.rand_vec(rng, 260, np.float64, 4))
+    Y_page = np.zeros((300, 4))
+    e.add_matrix_product_row_major("N", 1.0, X, 0.0, Y_page, 4)
+    Xp, Yp = torch.from_numpy(X.copy()).pin_memory(), torch.zeros(300, 4, dtype=torch.float64).pin_memory()
+    e.add_matrix_product_row_major("N", 1.0, Xp.numpy(), 0.0, Yp.numpy(), 4)
+    assert np.array_equal(Yp.numpy(), Y_page)
+    e.close()
