@@ -1,5 +1,6 @@
 // hmb200.cu -- C ABI of the engine (include/hmb200.h): create (plan + pack + upload), products, permutations.
 #include "hmb200.h"
+#include "internal.h"
 #include "planner.h"
 #include "../kernels/stream_kernels.cuh"
 #include "../kernels/mm_kernels.cuh"
@@ -14,6 +15,7 @@
 using namespace hmb200;
 
 static thread_local std::string g_last_error;
+void hmb200i_set_error(const char *msg) { g_last_error = msg ? msg : ""; }
 
 // ABI layout pinned (mirrored by htool_python_b200/_lib.py and checked in tests/test_capi_symbols.py)
 static_assert(sizeof(hmb200_flat) == 96 && sizeof(hmb200_options) == 64 && sizeof(hmb200_info) == 152, "hmb200 ABI layout changed");

@@ -43,6 +43,8 @@ def allgather_slabs_(buf, offs: List[int], sizes: List[int], mu: int, group=None
     every slab (MPI_Allgatherv of add_distributed_operator_vector_product_global_to_global.hpp:76)."""
     import torch.distributed as dist
 
+    if not dist.is_initialized():
+        return buf
     world = dist.get_world_size(group)
     if world == 1:
         return buf

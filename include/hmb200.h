@@ -144,6 +144,23 @@ int hmb200_matvec_user_z(hmb200_handle *h, const double *x, double *y, int mem);
 int hmb200_matmat_user_d(hmb200_handle *h, const double *X, double *Y, int mu, int mem);
 int hmb200_matmat_user_z(hmb200_handle *h, const double *X, double *Y, int mu, int mem);
 
+/* ---- Krylov vector kernels (device pointers only, asynchronous on `stream`) ---------------------------------------
+ * The BLAS-1/2 of the GMRES the reference's solver runs (DDM::solve -> HPDDM::IterativeMethod::GMRES,
+ * core/solvers/ddm.hpp:193, lib/hpddm/include/HPDDM_GMRES.hpp:30-196) on basis vectors that stay in HBM:
+ *   dots    h[j] = <V_j, w>, j < k                 (Blas::gemv 'C' of orthogonalization, lib/hpddm/include/HPDDM_iterative.hpp:541-548)
+ *   combine w += sign * sum_j h[j] V_j, *norm2 = ||w||^2   (Blas::gemv 'N' :551-552 and the dot of Arnoldi :738-739; with sign = +1
+ *           the basis combination of addSol :316-326)
+ *   axpby   out = alpha*x + beta*y, *norm2 = ||out||^2     (residual b - A x, HPDDM_GMRES.hpp:62-77)
+ *   scale   w /= sqrt(*norm2)                               (HPDDM_iterative.hpp:743-745)
+ * V holds basis vector j at V + j*ldv (elements); h, norm2 are DEVICE scalars (all-reduced between calls by the caller
+ * when the rows are distributed); norm2 may be NULL.  `scratch` must hold hmb200_krylov_scratch_elems(n, k) elements.
+ * Two-stage fixed-order reductions: results are bit-reproducible run to run. */
+int64_t hmb200_krylov_scratch_elems(int64_t n, int k);
+int hmb200_krylov_dots(const void *V, int64_t ldv, int k, const void *w, int64_t n, void *h, void *scratch, int elem_bytes, void *stream);
+int hmb200_krylov_combine(const void *V, int64_t ldv, int k, const void *h, double sign, void *w, int64_t n, double *norm2, void *scratch, int elem_bytes, void *stream);
+int hmb200_krylov_axpby(const double *alpha, const void *x, const double *beta, const void *y, void *out, int64_t n, double *norm2, void *scratch, int elem_bytes, void *stream);
+int hmb200_krylov_scale(void *w, int64_t n, const double *norm2, int elem_bytes, void *stream);
+
 /* timing of the kernels of the last product on the handle's stream (CUDA events), in milliseconds:
  * ms[0] phase 1 (t = V x), ms[1] partial reduce, ms[2] phase 2 (y += U t, y += D x), ms[3] whole product */
 int hmb200_last_kernel_ms(hmb200_handle *h, float ms[4]);

@@ -97,3 +97,78 @@ def test_partition_displacements_rejects_gaps():
     assert partition_displacements([(0, 3), (3, 4)]) == ([0, 3], [3, 4])
     with pytest.raises(ValueError):
         partition_displacements([(0, 3), (4, 4)])
+
+
+def _gmres_worker(rank, world, port, n, q):
+    """Host logic of the distributed solver on two `gloo` ranks: row-slab bookkeeping, input all-gather, all-reduced
+    dot products; the slab product and the vector algebra are numpy stand-ins (tests/numpy_space.py)."""
+    import torch.distributed as dist
+
+    from htool_python_b200 import FlatHMatrix, bridge
+    from htool_python_b200.distributed import partition_displacements
+    from htool_python_b200.solver import B200Solver
+    from numpy_space import NumpyKrylovSpace
+    from oracle import flat_oracle as fo
+    from oracle import gmres_oracle as go
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(11)
+        g = rng.standard_normal((3, n))
+        pts = np.asfortranarray(g / np.linalg.norm(g, axis=0))
+        tree = bridge.create_cluster_tree(pts, 2, world, 32)
+        offs, sizes = partition_displacements(tree.partition)
+        Hp = bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-6, eta=10.0, target_partition_number=rank, partition_number_for_symmetry=rank)
+        slab = FlatHMatrix.from_htool(Hp)
+        b = rng.random(n)
+        args = "-hpddm_krylov_method gmres -hpddm_tol 1e-6 -hpddm_gmres_restart 25 -hpddm_max_it 150 -hpddm_schwarz_method none -hpddm_variant right"
+        solver = B200Solver(None, space=NumpyKrylovSpace(slab, offs, sizes, rank, world))
+        x = np.zeros(n)
+        it = solver.solve(x, b, args)
+        # every rank must hold the same solution and iteration count; compare with the one-process oracle GMRES whose
+        # operator is the concatenation of the same slabs
+        slabs = [None] * world
+        dist.all_gather_object(slabs, (it, x))
+        if rank == 0:
+            ps, pt = slab.source_permutation, slab.target_permutation
+            flats = [slab] + [FlatHMatrix.from_htool(bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-6, eta=10.0, target_partition_number=p, partition_number_for_symmetry=p)) for p in range(1, world)]
+
+            def matvec(v):
+                vc = np.ascontiguousarray(v[ps])
+                yc = np.zeros(n)
+                for p, f in enumerate(flats):
+                    fo.add_vector_product(f, "N", 1.0, vc, 0.0, yc[offs[p]:offs[p] + sizes[p]])
+                y = np.empty(n)
+                y[pt] = yc
+                return y
+
+            x_ref, it_ref, info = go.gmres(matvec, b, **go.parse_hpddm_args(args))
+            same = all(s[0] == it and np.array_equal(s[1], x) for s in slabs)
+            q.put(("ok", (it, it_ref, same, rel_err(x, x_ref), np.linalg.norm(matvec(x) - b) / np.linalg.norm(b))))
+    except Exception:  # pragma: no cover
+        import traceback
+
+        q.put(("error", traceback.format_exc()))
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+def test_distributed_gmres_two_ranks_gloo():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gmres_worker, args=(r, 2, port, 1500, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    status, res = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+    assert status == "ok", res
+    it, it_ref, same, err, resid = res
+    assert it == it_ref and 0 < it < 150, (it, it_ref)
+    assert same
+    assert err < 1e-7 and resid < 2e-6, (err, resid)
