@@ -50,6 +50,8 @@ def parse():
     ap.add_argument("--wavenumber", type=float, default=0.0, help="helmholtz: k (default: 10 points per wavelength)")
     ap.add_argument("--rhs", type=int, default=1, help="right-hand sides per step (64 = BASELINE.json configs[3], DMMA multi-RHS path; off-metric)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gmres", action="store_true", help="also solve A x = b with the device-resident GMRES (BASELINE.json configs[4]; adds a 'gmres' object)")
+    ap.add_argument("--gmres-args", default="-hpddm_krylov_method gmres -hpddm_schwarz_method none -hpddm_variant right -hpddm_tol 1e-6 -hpddm_gmres_restart 40 -hpddm_max_it 200")
     ap.add_argument("--engine-opts", default="", help="k=v,k=v overrides of hmb200_options (tuning runs)")
     return ap.parse_args()
 
@@ -215,7 +217,12 @@ def run_b200(args):
     else:
         def step():
             engine.add_vector_product("N", 1.0, x_cluster, 0.0, y_cluster)
-    apply_user = (lambda: op @ x_user) if mu > 1 else (lambda: op * x_user)
+    if mu > 1:
+        apply_user = lambda: op @ x_user  # noqa: E731
+    else:  # page-locked host buffers (torch pin_memory): the library DMAs straight from / into them
+        x_pin = torch.from_numpy(np.ascontiguousarray(x_user)).pin_memory().numpy()
+        y_pin = torch.zeros(n, dtype=tdt).pin_memory().numpy()
+        apply_user = lambda: op.matvec(x_pin, out=y_pin)  # noqa: E731
 
     # ---- device-resident timed region ------------------------------------------------------------------------
     for _ in range(args.warmup):
@@ -254,6 +261,11 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_step = float(t.item()) / args.steps
+
+    # ---- GMRES with the Krylov basis resident on the device (off-metric extra) -----------------------------------------
+    gm = None
+    if args.gmres and mu == 1:
+        gm = run_gmres(args, op, flat, tree, H, world, rank, dev, thr, log, barrier)
 
     # ---- roofline of the dominant kernel (max over ranks of its time; this rank's bytes) ---------------------------
     w1, w2 = w_split(flat)
@@ -315,11 +327,54 @@ def run_b200(args):
             "cpu_baseline": cpu,
             "parity_rel_err_vs_reference": parity,
         }
+        line["config"]["e2e_api"] = "B200HMatrix.matvec(x, out) / B200DistributedOperator.matvec(x, out) on page-locked host numpy buffers, user numbering"
+        if gm is not None:
+            line["gmres"] = gm
         print(json.dumps(line), flush=True)
     barrier()
     op.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_gmres(args, op, flat, tree, H, world, rank, dev, threads, log, barrier):
+    """b = A x_ref, then GMRES from x = 0 with HPDDM's options; device solver vs (rank 0, N=1) the reference's HPDDM GMRES
+    (oracle/_ref/libhpddm_ref.so) driving the reference's OpenMP product on the host cores."""
+    import torch
+
+    from htool_python_b200 import B200DistributedOperator, B200Solver
+
+    n = args.n
+    dop = op if world > 1 else B200DistributedOperator.from_engine(op.engine, flat)
+    solver = B200Solver(dop)
+    x_ref = np.random.default_rng(3).random(n)
+    b = dop.matvec(x_ref)
+    x = np.zeros(n)
+    solver.solve(x, b, args.gmres_args + " -hpddm_max_it 3")  # warm-up (allocations, NCCL)
+    x[:] = 0
+    barrier()
+    t0 = time.perf_counter()
+    it = solver.solve(x, b, args.gmres_args)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    res = float(np.linalg.norm(dop.matvec(x) - b) / np.linalg.norm(b))
+    out = {"iterations": int(it), "operator_calls": int(solver.last_info["operator_calls"]), "solve_s": round(dt, 4), "true_residual": res,
+           "args": args.gmres_args, "n": n, "n_gpus": world, "ms_per_iteration": round(1e3 * dt / max(it, 1), 3)}
+    log(f"gmres: {it} iterations, {dt:.3f} s, true residual {res:.2e}")
+    if world == 1 and not args.no_cpu_baseline:
+        import helpers_ref
+
+        ro = helpers_ref.ref_ops()
+        ro.omp_set_num_threads(threads)
+        fn = getattr(ro, "vector_product_user_addr_" + flat.dtype)
+        t0 = time.perf_counter()
+        x_cpu, it_cpu, calls_cpu = helpers_ref.hpddm_solve(lambda v: fn(H.address, np.ascontiguousarray(v), True), b, args=args.gmres_args)
+        dt_cpu = time.perf_counter() - t0
+        out.update({"reference_iterations": int(it_cpu), "reference_operator_calls": int(calls_cpu), "reference_solve_s": round(dt_cpu, 3),
+                    "reference_cores": threads, "solution_rel_diff_vs_reference": float(np.linalg.norm(x - x_cpu) / np.linalg.norm(x_cpu)),
+                    "reference": "HPDDM::IterativeMethod::GMRES (lib/hpddm, compiled from the reference sources) + reference OpenMP product"})
+        log(f"gmres reference (CPU, {threads} threads): {it_cpu} iterations, {dt_cpu:.2f} s")
+    return out
 
 
 def cpu_reference_product(H, flat, x_user, threads, budget_s, log):

@@ -69,7 +69,12 @@ class B200DistributedOperator:
     partition : [(offset, size)] of every rank's slab in target cluster numbering
     """
 
-    def __init__(self, slab_flat, partition, group=None, device: Optional[int] = None, **options):
+    @classmethod
+    def from_engine(cls, engine, flat, group=None):
+        """single-process operator over an EXISTING engine (e.g. `B200HMatrix(...).engine`): nothing is packed or uploaded again"""
+        return cls(flat, [(0, flat.n_rows)], group=group, device=engine.device, engine=engine)
+
+    def __init__(self, slab_flat, partition, group=None, device: Optional[int] = None, engine=None, **options):
         import torch
         import torch.distributed as dist
 
@@ -85,7 +90,8 @@ class B200DistributedOperator:
             raise ValueError("slab_flat is not this rank's slab of the partition")
         self.n_target = sum(self.sizes)
         self.n_source = slab_flat.n_cols
-        self.engine = Engine(slab_flat, device=device, **options)
+        self._owns_engine = engine is None
+        self.engine = engine if engine is not None else Engine(slab_flat, device=device, **options)
         self.device = torch.device("cuda", self.engine.device)
         self.is_complex = self.engine.is_complex
         self.np_dtype = self.engine.np_dtype
@@ -146,6 +152,11 @@ class B200DistributedOperator:
         return self._x[mu], self._pin[mu]
 
     def __mul__(self, x):
+        return self.matvec(x)
+
+    def matvec(self, x, out=None):
+        """`A * x` (user numbering, host arrays); `out`, when given, receives the result in place.  Page-locked numpy buffers
+        (`torch.Tensor.pin_memory().numpy()`) are DMA'd directly, pageable ones go through the operator's pinned staging."""
         import torch
 
         x = np.asarray(x)
@@ -153,16 +164,38 @@ class B200DistributedOperator:
             raise RuntimeError("Wrong dimension for HMatrix-vector product")  # distributed_operator.hpp:25-27
         if x.shape[0] != self.n_source:
             raise RuntimeError("Wrong size for HMatrix-vector product")
+        if out is not None and (not isinstance(out, np.ndarray) or out.dtype != self.np_dtype or out.shape != (self.n_target,) or not out.flags.c_contiguous):
+            raise ValueError("out must be a contiguous numpy array of the operator's dtype and target size")
         (xu, xc, yc, yu), (pin_x, pin_y) = self._buffers(1)
         with torch.cuda.device(self.device):
-            pin_x.numpy()[:] = x.astype(self.np_dtype, copy=False)
-            xu.copy_(pin_x, non_blocking=True)
+            src = self._as_pinned_tensor(x)
+            if src is None:
+                pin_x.numpy()[:] = x.astype(self.np_dtype, copy=False)
+                src = pin_x
+            xu.copy_(src, non_blocking=True)
             self._permute(True, self.perm_s, self.n_source, xu, xc, 1)     # global_to_root_cluster (:108)
             self.matvec_cluster_(xc, yc)
             self._permute(False, self.perm_t, self.n_target, yc, yu, 1)    # root_cluster_to_global (:117)
-            pin_y.copy_(yu, non_blocking=True)
+            dst = self._as_pinned_tensor(out) if out is not None else None
+            (dst if dst is not None else pin_y).copy_(yu, non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
-        return pin_y.numpy().copy()
+        if out is None:
+            return pin_y.numpy().copy()
+        if dst is None:
+            out[:] = pin_y.numpy()
+        return out
+
+    def _as_pinned_tensor(self, a):
+        """torch view of a page-locked, contiguous numpy array of the operator's dtype (None otherwise)"""
+        import torch
+
+        if not isinstance(a, np.ndarray) or a.dtype != self.np_dtype or not a.flags.c_contiguous:
+            return None
+        try:
+            t = torch.from_numpy(a)
+            return t if t.is_pinned() else None
+        except Exception:
+            return None
 
     def __matmul__(self, X):
         """X: (n_source, mu) Fortran-ordered like the reference (distributed_operator.hpp:39-65); result F-ordered."""
@@ -191,4 +224,5 @@ class B200DistributedOperator:
         return np.array(pin_y.numpy().reshape((self.n_target, mu), order="F"), order="F")
 
     def close(self):
-        self.engine.close()
+        if self._owns_engine:
+            self.engine.close()

@@ -51,6 +51,21 @@ class B200HMatrix:
         x = np.ascontiguousarray(x, dtype=self._np_dtype)  # forcecast, like py::array_t<T, f_style>
         return self.engine.matvec_user(x)
 
+    def matvec(self, x, out=None):
+        """`H * x` writing into the caller's `out` (user numbering).  With page-locked numpy buffers (e.g.
+        `torch.empty(n, dtype=torch.float64).pin_memory().numpy()`) the library DMAs straight from / into them and the
+        call makes no host-side copy at all; pageable buffers go through the pinned staging area."""
+        if _is_torch(x):
+            return self.engine.matvec_user(x.contiguous(), out)
+        x = np.asarray(x)
+        if x.ndim != 1:
+            raise RuntimeError("Wrong dimension for HMatrix-vector product")
+        if x.shape[0] != self.shape[1]:
+            raise RuntimeError("Wrong size for HMatrix-vector product")
+        if x.dtype != self._np_dtype or not x.flags.c_contiguous:
+            x = np.ascontiguousarray(x, dtype=self._np_dtype)
+        return self.engine.matvec_user(x, out)
+
     # Y = H @ X  (user numbering, Fortran-ordered result like the reference)
     def __matmul__(self, X):
         X = np.asarray(X)

@@ -19,7 +19,7 @@ TOL = 1e-12  # BASELINE.json north_star: relative 2-norm, reordered summation al
 
 
 def golden_names():
-    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "*.npz")))
+    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "[dz]_*.npz")))  # H-matrix fixtures
 
 
 def load_golden(name):
