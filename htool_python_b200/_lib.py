@@ -31,6 +31,7 @@ EXPORTS = {
     "hmb200_destroy": (None, [c_void_p]),
     "hmb200_get_info": (c_int, [c_void_p, POINTER(hmb200_info)]),
     "hmb200_set_stream": (c_int, [c_void_p, c_void_p]),
+    "hmb200_set_graphs": (c_int, [c_void_p, c_int]),
     "hmb200_add_vector_product_d": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int]),
     "hmb200_add_vector_product_z": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int]),
     "hmb200_add_matrix_product_row_major_d": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int]),

@@ -8,6 +8,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -79,6 +80,16 @@ struct hmb200_handle {
     void *xsub = nullptr; // zero-extended source window of add_sub_matrix_product_to_local
     uint64_t xsub_elems = 0;
     int target_offset = 0, source_offset = 0; // offsets of the root block in the target / source tree numbering
+    // CUDA graphs of the device-resident product: one instantiated graph per (op, in, out, alpha, beta), captured on a private
+    // stream the second time a key is seen and replayed on the caller's stream (removes ~20 us of launch latency per product)
+    struct GraphKey {
+        char op; const void *in; void *out; double a[2], b[2]; int fused;
+        bool operator<(const GraphKey &o) const { return std::memcmp(this, &o, sizeof(GraphKey)) < 0; }
+    };
+    struct GraphEntry { cudaGraphExec_t exec = nullptr; int64_t launches = 0; int seen = 0; };
+    std::map<GraphKey, GraphEntry> graphs;
+    cudaStream_t cap_stream = nullptr;
+    bool use_graphs = true;
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
     uint32_t *counters = nullptr; // [2]
@@ -429,6 +440,12 @@ int collect_timing(hmb200_handle *h, float ms[4], bool last_only) {
     return n;
 }
 
+void clear_graphs(hmb200_handle *h) {
+    for (auto &kv : h->graphs)
+        if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    h->graphs.clear();
+}
+
 template <typename T>
 int vector_product(hmb200_handle *h, char trans, const double *alpha, const void *in, const double *beta, void *out, int mem) {
     CUDA_CHECK(cudaSetDevice(h->device));
@@ -436,8 +453,50 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
     const size_t in_b = (size_t)po.n_in * sizeof(T), out_b = (size_t)po.n_out * sizeof(T);
     const bool beta_zero = beta[0] == 0.0 && (h->es == 8 || beta[1] == 0.0);
     if (mem == HMB200_DEVICE) {
-        CUDA_CHECK(cudaMemcpyAsync(h->xz, in, in_b, cudaMemcpyDeviceToDevice, h->stream));
-        run_product<T>(h, po, alpha, beta, out, nullptr);
+        auto issue = [&] {
+            CUDA_CHECK(cudaMemcpyAsync(h->xz, in, in_b, cudaMemcpyDeviceToDevice, h->stream));
+            run_product<T>(h, po, alpha, beta, out, nullptr);
+        };
+        if (!h->use_graphs || h->timing) {
+            issue();
+        } else {
+            hmb200_handle::GraphKey key;
+            std::memset(&key, 0, sizeof(key));
+            key.op = po.op; key.in = in; key.out = out;
+            key.a[0] = alpha[0]; key.a[1] = h->es == 16 ? alpha[1] : 0.0; key.b[0] = beta[0]; key.b[1] = h->es == 16 ? beta[1] : 0.0;
+            if (h->graphs.size() > 256) clear_graphs(h);
+            auto &ge = h->graphs[key];
+            if (!ge.exec && ++ge.seen < 2) {
+                issue(); // first use of a key runs eagerly (one-off pointers never pay for a capture)
+            } else {
+                if (!ge.exec) {
+                    if (!h->cap_stream) CUDA_CHECK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+                    cudaStream_t user = h->stream;
+                    const int64_t l0 = h->launches;
+                    cudaGraph_t g = nullptr;
+                    CUDA_CHECK(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+                    h->stream = h->cap_stream;
+                    try {
+                        issue();
+                    } catch (...) {
+                        h->stream = user;
+                        cudaStreamEndCapture(h->cap_stream, &g);
+                        if (g) cudaGraphDestroy(g);
+                        h->graphs.erase(key);
+                        throw;
+                    }
+                    h->stream = user;
+                    CUDA_CHECK(cudaStreamEndCapture(h->cap_stream, &g));
+                    ge.launches = h->launches - l0;
+                    h->launches = l0;
+                    cudaError_t ie = cudaGraphInstantiate(&ge.exec, g, 0);
+                    cudaGraphDestroy(g);
+                    if (ie != cudaSuccess) { h->graphs.erase(key); throw std::runtime_error(std::string("cudaGraphInstantiate failed: ") + cudaGetErrorString(ie)); }
+                }
+                CUDA_CHECK(cudaGraphLaunch(ge.exec, h->stream));
+                h->launches += ge.launches;
+            }
+        }
     } else {
         ensure_pinned(h, in_b + out_b + 64);
         ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out, h->es);
@@ -694,6 +753,8 @@ void hmb200_destroy(hmb200_handle *h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream); else cudaDeviceSynchronize();
+    clear_graphs(h);
+    if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     for (auto &po : h->ops) free_op(po);
     cudaFree(h->xz);
     cudaFree(h->ybuf);
@@ -733,6 +794,12 @@ int hmb200_add_matrix_product_row_major_d(hmb200_handle *h, char trans, const do
 }
 int hmb200_add_matrix_product_row_major_z(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mu, int mem) {
     return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return matrix_product<double2>(h, trans, alpha, in, beta, out, mu, mem); });
+}
+int hmb200_set_graphs(hmb200_handle *h, int on) {
+    if (!h) { g_last_error = "null handle"; return 1; }
+    h->use_graphs = on != 0;
+    if (!on) clear_graphs(h);
+    return 0;
 }
 int hmb200_set_cluster_offsets(hmb200_handle *h, int target_offset, int source_offset) {
     if (!h) { g_last_error = "null handle"; return 1; }

@@ -101,6 +101,9 @@ hmb200_handle *hmb200_create_z(const hmb200_flat *flat, int device, void *stream
 void hmb200_destroy(hmb200_handle *h);
 int hmb200_get_info(const hmb200_handle *h, hmb200_info *info);
 int hmb200_set_stream(hmb200_handle *h, void *stream);
+/* device-resident single-RHS products are replayed from CUDA graphs (one per (op, in, out, alpha, beta), captured the
+ * second time a combination is seen); on by default, 0 turns it off */
+int hmb200_set_graphs(hmb200_handle *h, int on);
 
 /* ---- products (cluster numbering) ------------------------------------------------------------------------------
  * Replaces VirtualGlobalToLocalOperator::add_vector_product

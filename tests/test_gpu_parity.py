@@ -381,3 +381,42 @@ def test_page_locked_host_buffers_skip_staging():
     e.add_matrix_product_row_major("N", 1.0, Xp.numpy(), 0.0, Yp.numpy(), 4)
     assert np.array_equal(Yp.numpy(), Y_page)
     e.close()
+
+
+def test_device_products_replayed_from_cuda_graphs():
+    """device-resident products: 1st call eager, 2nd captured into a CUDA graph, later calls replayed -- all bit-identical;
+    changing alpha / beta / pointers selects another graph; the launch counter keeps counting kernels."""
+    import torch
+
+    rng = np.random.default_rng(91)
+    flat = synthetic_flat(rng, 700, 650, max_leaf=64)
+    e = _engine(flat)
+    x = torch.from_numpy(helpers.rand_vec(rng, 650, np.float64)).cuda()
+    y0 = torch.from_numpy(helpers.rand_vec(rng, 700, np.float64)).cuda()
+    y_ref = y0.cpu().numpy().copy()
+    fo.add_vector_product(flat, "N", 1.5, x.cpu().numpy(), -0.25, y_ref)
+    outs = []
+    y = torch.empty_like(y0)
+    l0 = e.launch_count
+    for _ in range(5):
+        y.copy_(y0)
+        e.add_vector_product("N", 1.5, x, -0.25, y)
+        outs.append(y.cpu().numpy().copy())
+    per_call = (e.launch_count - l0) // 5
+    assert per_call >= 2 and e.launch_count - l0 == 5 * per_call
+    assert rel_err(outs[0], y_ref) < TOL
+    assert all(np.array_equal(o, outs[0]) for o in outs[1:])
+    # other scalars / other buffers after the graph exists
+    x2 = torch.from_numpy(helpers.rand_vec(rng, 650, np.float64)).cuda()
+    for xv, a, b in [(x, 2.0, 0.0), (x2, 1.5, -0.25), (x2, 1.5, -0.25), (x2, 1.5, -0.25)]:
+        y.copy_(y0)
+        e.add_vector_product("N", a, xv, b, y)
+        r = y0.cpu().numpy().copy()
+        fo.add_vector_product(flat, "N", a, xv.cpu().numpy(), b, r)
+        assert rel_err(y.cpu().numpy(), r) < TOL
+    _lib_check = __import__("htool_python_b200")._lib
+    _lib_check.check(_lib_check.lib().hmb200_set_graphs(e._h, 0))
+    y.copy_(y0)
+    e.add_vector_product("N", 1.5, x, -0.25, y)
+    assert np.array_equal(y.cpu().numpy(), outs[0])
+    e.close()
