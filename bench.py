@@ -211,6 +211,9 @@ def run_b200(args):
     elif mu > 1:
         def step():
             engine.add_matrix_product_row_major("N", 1.0, x_cluster, 0.0, y_cluster, mu)
+    elif world > 1 and op.fused:
+        def step():  # slab product whose phase-2 epilogue stores the rows into every rank's replicated vector (no NCCL call)
+            op.matvec_cluster_fused_(x_cluster)
     elif world > 1:
         def step():
             op.matvec_cluster_(x_cluster, y_cluster)
@@ -228,7 +231,6 @@ def run_b200(args):
     for _ in range(args.warmup):
         step()
     barrier()
-    engine.enable_timing(True)  # per-kernel CUDA events on the launching stream, collected after the region
     launches0 = engine.launch_count
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -241,12 +243,20 @@ def run_b200(args):
     clocks = sampler.result()
     ms_total = ev0.elapsed_time(ev1)
     launches = engine.launch_count - launches0
-    kms = engine.kernel_ms_avg()
-    engine.enable_timing(False)
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
+    # per-kernel durations: the SAME steps once more with CUDA events recorded around every kernel on the launching stream
+    # (the timed region above replays CUDA graphs, which carry no per-kernel events)
+    engine.enable_timing(True)
+    for _ in range(args.steps):
+        step()
+    barrier()
+    kms = engine.kernel_ms_avg()
+    engine.enable_timing(False)
+    if world > 1 and op.fused and op.peer_status() != 0:
+        raise SystemExit(f"bench.py: rank {rank}: a peer did not publish its epoch (status {op.peer_status()})")
 
     # ---- end to end through the public API with host buffers ----------------------------------------------------
     for _ in range(2):
@@ -316,7 +326,9 @@ def run_b200(args):
             "data": "synthetic",
             "config": {"workload": f"{WORKLOADS[args.kernel]} H-matrix, N={n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
                                    f"leaf {args.leaf}, {'single-RHS matvec' if mu == 1 else str(mu) + '-RHS matmat (DMMA path)'} (BASELINE.json configs[{(1 if mu == 1 else 3) if args.kernel == 'laplace' else 2}])",
-                       "rhs_per_step": mu, "partition": f"block-row slabs x{world}", "l2": "inputs larger than L2 (factor stream >> 126 MB, read once per step)",
+                       "rhs_per_step": mu, "partition": f"block-row slabs x{world}",
+                       "allgather": ("none (1 GPU)" if world == 1 else "fused into the phase-2 epilogue: peer stores over NVLink + epoch flags (CUDA IPC)" if (mu == 1 and op.fused) else "NCCL all-gather"),
+                       "launch": "CUDA graph replay of the product (captured by libhmb200.so)" if mu == 1 else "eager", "l2": "inputs larger than L2 (factor stream >> 126 MB, read once per step)",
                        "stored_coefficients_rank0": flat.stored_coefficients, "leaves_rank0": flat.n_leaves,
                        "assembly": "reference HMatrixTreeBuilder (OpenMP, native generator), outside the timed region", **build_t},
             "clocks": clocks,

@@ -39,6 +39,12 @@ EXPORTS = {
     "hmb200_set_cluster_offsets": (c_int, [c_void_p, c_int, c_int]),
     "hmb200_add_sub_matrix_product_to_local_d": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int]),
     "hmb200_add_sub_matrix_product_to_local_z": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int]),
+    "hmb200_peer_create": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_void_p]),
+    "hmb200_peer_attach": (c_int, [c_void_p, c_void_p]),
+    "hmb200_peer_buffer": (c_int, [c_void_p, c_int, POINTER(c_void_p)]),
+    "hmb200_peer_status": (c_int, [c_void_p, POINTER(c_int)]),
+    "hmb200_vector_product_allgather_d": (c_int, [c_void_p, c_void_p, c_void_p, POINTER(c_void_p)]),
+    "hmb200_vector_product_allgather_z": (c_int, [c_void_p, c_void_p, c_void_p, POINTER(c_void_p)]),
     "hmb200_permute_gather": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "hmb200_permute_scatter": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "hmb200_set_permutations": (c_int, [c_void_p, c_void_p, c_void_p]),

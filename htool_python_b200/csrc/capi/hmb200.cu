@@ -90,6 +90,16 @@ struct hmb200_handle {
     std::map<GraphKey, GraphEntry> graphs;
     cudaStream_t cap_stream = nullptr;
     bool use_graphs = true;
+    // fused all-gather: one IPC-shared region per rank = [replicated y, buffer 0 | buffer 1 | control block]; the control
+    // block holds flags[2][8] (written by the peers), and -- local use only -- epoch[2], the CTA counter and the error word
+    struct Peer {
+        int n_ranks = 0, rank = 0, slab_offset = 0;
+        int64_t n_global = 0;
+        size_t buf_bytes = 0, region_bytes = 0;
+        uint8_t *region[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; // [rank] own allocation, others IPC-mapped
+        bool attached = false;
+        uint64_t products = 0;
+    } peer;
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
     uint32_t *counters = nullptr; // [2]
@@ -374,8 +384,18 @@ PackedOp &select_op(hmb200_handle *h, char trans) {
 }
 
 // runs out = beta*out + alpha*op(A)*xz[0:n_in] on the handle's stream; x must already be in xz; y is a device pointer
+// control block of rank q's shared region (after the two replicated buffers)
+inline unsigned long long *peer_ctrl_flags(const hmb200_handle::Peer &pr, int q, int buf) {
+    return reinterpret_cast<unsigned long long *>(pr.region[q] + 2 * pr.buf_bytes) + 8 * buf;
+}
+inline unsigned long long *peer_ctrl_epoch(const hmb200_handle::Peer &pr, int buf) {
+    return reinterpret_cast<unsigned long long *>(pr.region[pr.rank] + 2 * pr.buf_bytes + 128) + buf;
+}
+inline uint32_t *peer_ctrl_done(const hmb200_handle::Peer &pr) { return reinterpret_cast<uint32_t *>(pr.region[pr.rank] + 2 * pr.buf_bytes + 160); }
+inline int *peer_ctrl_err(const hmb200_handle::Peer &pr) { return reinterpret_cast<int *>(pr.region[pr.rank] + 2 * pr.buf_bytes + 192); }
+
 template <typename T>
-void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, void *y, const int32_t *out_perm) {
+void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, void *y, const int32_t *out_perm, int peer_buf = -1) {
     const Options &o = h->opt;
     const int threads = (o.consumer_warps + 1) * 32;
     const int ctas    = o.ctas > 0 ? o.ctas : h->n_sms;
@@ -412,6 +432,16 @@ void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const doub
     if (po.n_units[1] > 0) {
         p.stream = po.stream[1]; p.stages = po.stages[1]; p.zcopies = po.zcopies[1]; p.units = po.units[1];
         p.n_units = po.n_units[1]; p.n_zcopies = po.n_zcopies[1]; p.counter = h->counters + 1;
+        if (peer_buf >= 0) { // replicate the slab into every rank's buffer `peer_buf` and publish the epoch
+            const hmb200_handle::Peer &pr = h->peer;
+            const size_t slab_b = (size_t)pr.slab_offset * sizeof(T);
+            for (int q = 0; q < pr.n_ranks; q++) {
+                if (q != pr.rank) p.peer_y[p.n_peers++] = pr.region[q] + (size_t)peer_buf * pr.buf_bytes + slab_b;
+                p.peer_flags[p.n_flags++] = peer_ctrl_flags(pr, q, peer_buf) + pr.rank;
+            }
+            p.epoch = peer_ctrl_epoch(pr, peer_buf);
+            p.done  = peer_ctrl_done(pr);
+        }
         size_t smem = stream_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_bytes, o.n_stages, o.consumer_warps);
         hmatrix_stream_kernel<T, 2><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]), threads, smem, h->stream>>>(p);
         h->launches++;
@@ -446,6 +476,51 @@ void clear_graphs(hmb200_handle *h) {
     h->graphs.clear();
 }
 
+// issues `issue()` (a stream-ordered sequence on h->stream without host synchronisation) either eagerly or -- from the second
+// time `key` is seen -- as a replay of a CUDA graph captured on a private stream
+template <typename F>
+void run_cached(hmb200_handle *h, const hmb200_handle::GraphKey &key, F &&issue) {
+    if (!h->use_graphs || h->timing) {
+        issue();
+        return;
+    }
+    if (h->graphs.size() > 256) clear_graphs(h);
+    auto &ge = h->graphs[key];
+    if (!ge.exec && ++ge.seen < 2 && key.fused == 0) {
+        issue(); // first use of a key runs eagerly (one-off pointers never pay for a capture); fused products always recur
+        return;
+    }
+    if (!ge.exec) {
+        if (!h->cap_stream) CUDA_CHECK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+        cudaStream_t user = h->stream;
+        const int64_t l0 = h->launches;
+        cudaGraph_t g = nullptr;
+        CUDA_CHECK(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+        h->stream = h->cap_stream;
+        try {
+            issue();
+        } catch (...) {
+            h->stream = user;
+            cudaStreamEndCapture(h->cap_stream, &g);
+            if (g) cudaGraphDestroy(g);
+            h->graphs.erase(key);
+            throw;
+        }
+        h->stream = user;
+        CUDA_CHECK(cudaStreamEndCapture(h->cap_stream, &g));
+        ge.launches = h->launches - l0;
+        h->launches = l0;
+        cudaError_t ie = cudaGraphInstantiate(&ge.exec, g, 0);
+        cudaGraphDestroy(g);
+        if (ie != cudaSuccess) {
+            h->graphs.erase(key);
+            throw std::runtime_error(std::string("cudaGraphInstantiate failed: ") + cudaGetErrorString(ie));
+        }
+    }
+    CUDA_CHECK(cudaGraphLaunch(ge.exec, h->stream));
+    h->launches += ge.launches;
+}
+
 template <typename T>
 int vector_product(hmb200_handle *h, char trans, const double *alpha, const void *in, const double *beta, void *out, int mem) {
     CUDA_CHECK(cudaSetDevice(h->device));
@@ -453,50 +528,14 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
     const size_t in_b = (size_t)po.n_in * sizeof(T), out_b = (size_t)po.n_out * sizeof(T);
     const bool beta_zero = beta[0] == 0.0 && (h->es == 8 || beta[1] == 0.0);
     if (mem == HMB200_DEVICE) {
-        auto issue = [&] {
+        hmb200_handle::GraphKey key;
+        std::memset(&key, 0, sizeof(key));
+        key.op = po.op; key.in = in; key.out = out;
+        key.a[0] = alpha[0]; key.a[1] = h->es == 16 ? alpha[1] : 0.0; key.b[0] = beta[0]; key.b[1] = h->es == 16 ? beta[1] : 0.0;
+        run_cached(h, key, [&] {
             CUDA_CHECK(cudaMemcpyAsync(h->xz, in, in_b, cudaMemcpyDeviceToDevice, h->stream));
             run_product<T>(h, po, alpha, beta, out, nullptr);
-        };
-        if (!h->use_graphs || h->timing) {
-            issue();
-        } else {
-            hmb200_handle::GraphKey key;
-            std::memset(&key, 0, sizeof(key));
-            key.op = po.op; key.in = in; key.out = out;
-            key.a[0] = alpha[0]; key.a[1] = h->es == 16 ? alpha[1] : 0.0; key.b[0] = beta[0]; key.b[1] = h->es == 16 ? beta[1] : 0.0;
-            if (h->graphs.size() > 256) clear_graphs(h);
-            auto &ge = h->graphs[key];
-            if (!ge.exec && ++ge.seen < 2) {
-                issue(); // first use of a key runs eagerly (one-off pointers never pay for a capture)
-            } else {
-                if (!ge.exec) {
-                    if (!h->cap_stream) CUDA_CHECK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
-                    cudaStream_t user = h->stream;
-                    const int64_t l0 = h->launches;
-                    cudaGraph_t g = nullptr;
-                    CUDA_CHECK(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
-                    h->stream = h->cap_stream;
-                    try {
-                        issue();
-                    } catch (...) {
-                        h->stream = user;
-                        cudaStreamEndCapture(h->cap_stream, &g);
-                        if (g) cudaGraphDestroy(g);
-                        h->graphs.erase(key);
-                        throw;
-                    }
-                    h->stream = user;
-                    CUDA_CHECK(cudaStreamEndCapture(h->cap_stream, &g));
-                    ge.launches = h->launches - l0;
-                    h->launches = l0;
-                    cudaError_t ie = cudaGraphInstantiate(&ge.exec, g, 0);
-                    cudaGraphDestroy(g);
-                    if (ie != cudaSuccess) { h->graphs.erase(key); throw std::runtime_error(std::string("cudaGraphInstantiate failed: ") + cudaGetErrorString(ie)); }
-                }
-                CUDA_CHECK(cudaGraphLaunch(ge.exec, h->stream));
-                h->launches += ge.launches;
-            }
-        }
+        });
     } else {
         ensure_pinned(h, in_b + out_b + 64);
         ensure_dev(&h->ybuf, &h->ybuf_elems, (uint64_t)po.n_out, h->es);
@@ -715,6 +754,35 @@ int matvec_user(hmb200_handle *h, const void *x, void *y, int mem, int mu) {
     return 0;
 }
 
+// y_replicated = alpha * A_slab * in on EVERY rank: the slab product whose phase-2 epilogue stores each output row into the
+// replicated vector of all ranks (peer memory over NVLink), then a wait for the epochs of all ranks.  Buffers alternate so
+// that a rank running one product ahead never overwrites a vector its peers may still be reading.
+template <typename T>
+int fused_product(hmb200_handle *h, const double *alpha, const void *in, void **y_out) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    hmb200_handle::Peer &pr = h->peer;
+    if (!pr.attached) throw std::runtime_error("hmb200_peer_attach has not been called");
+    PackedOp &po = h->ops[0];
+    const int buf = (int)(pr.products & 1);
+    pr.products++;
+    uint8_t *ybuf = pr.region[pr.rank] + (size_t)buf * pr.buf_bytes;
+    const double zero[2] = {0.0, 0.0};
+    const size_t in_b = (size_t)po.n_in * sizeof(T);
+    hmb200_handle::GraphKey key;
+    std::memset(&key, 0, sizeof(key));
+    key.op = 'N'; key.in = in; key.out = ybuf; key.fused = 1 + buf;
+    key.a[0] = alpha[0]; key.a[1] = h->es == 16 ? alpha[1] : 0.0;
+    run_cached(h, key, [&] {
+        CUDA_CHECK(cudaMemcpyAsync(h->xz, in, in_b, cudaMemcpyDeviceToDevice, h->stream));
+        run_product<T>(h, po, alpha, zero, ybuf + (size_t)pr.slab_offset * sizeof(T), nullptr, buf);
+        peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), 4000000000ll);
+        h->launches++;
+        CUDA_CHECK(cudaGetLastError());
+    });
+    if (y_out) *y_out = ybuf;
+    return 0;
+}
+
 template <typename F>
 int guarded(F &&f) {
     try {
@@ -755,6 +823,10 @@ void hmb200_destroy(hmb200_handle *h) {
     if (h->stream) cudaStreamSynchronize(h->stream); else cudaDeviceSynchronize();
     clear_graphs(h);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
+    for (int q = 0; q < h->peer.n_ranks; q++) {
+        if (!h->peer.region[q]) continue;
+        if (q == h->peer.rank) cudaFree(h->peer.region[q]); else cudaIpcCloseMemHandle(h->peer.region[q]);
+    }
     for (auto &po : h->ops) free_op(po);
     cudaFree(h->xz);
     cudaFree(h->ybuf);
@@ -794,6 +866,66 @@ int hmb200_add_matrix_product_row_major_d(hmb200_handle *h, char trans, const do
 }
 int hmb200_add_matrix_product_row_major_z(hmb200_handle *h, char trans, const double *alpha, const double *in, const double *beta, double *out, int mu, int mem) {
     return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return matrix_product<double2>(h, trans, alpha, in, beta, out, mu, mem); });
+}
+int hmb200_peer_create(hmb200_handle *h, int n_ranks, int rank, int64_t n_global, int slab_offset, unsigned char *ipc_handle_out) {
+    return guarded([&] {
+        if (!h || !ipc_handle_out) throw std::runtime_error("null argument");
+        if (n_ranks < 1 || n_ranks > kMaxPeers || rank < 0 || rank >= n_ranks) throw std::runtime_error("between 1 and 8 ranks are supported");
+        if (slab_offset < 0 || (int64_t)slab_offset + h->n_rows > n_global) throw std::runtime_error("slab does not fit the replicated vector");
+        CUDA_CHECK(cudaSetDevice(h->device));
+        hmb200_handle::Peer &pr = h->peer;
+        if (pr.region[pr.rank]) throw std::runtime_error("peer region already created");
+        pr.n_ranks = n_ranks; pr.rank = rank; pr.n_global = n_global; pr.slab_offset = slab_offset;
+        pr.buf_bytes    = (((size_t)n_global * h->es) + 255) & ~(size_t)255;
+        pr.region_bytes = 2 * pr.buf_bytes + 256;
+        void *r = nullptr;
+        CUDA_CHECK(cudaMalloc(&r, pr.region_bytes));
+        CUDA_CHECK(cudaMemset(r, 0, pr.region_bytes));
+        pr.region[rank] = (uint8_t *)r;
+        cudaIpcMemHandle_t ih;
+        CUDA_CHECK(cudaIpcGetMemHandle(&ih, r));
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+        std::memcpy(ipc_handle_out, &ih, 64);
+        return 0;
+    });
+}
+int hmb200_peer_attach(hmb200_handle *h, const unsigned char *ipc_handles) {
+    return guarded([&] {
+        if (!h) throw std::runtime_error("null handle");
+        hmb200_handle::Peer &pr = h->peer;
+        if (!pr.region[pr.rank]) throw std::runtime_error("hmb200_peer_create has not been called");
+        if (pr.n_ranks > 1 && !ipc_handles) throw std::runtime_error("null argument");
+        CUDA_CHECK(cudaSetDevice(h->device));
+        for (int q = 0; q < pr.n_ranks; q++) {
+            if (q == pr.rank || pr.region[q]) continue;
+            cudaIpcMemHandle_t ih;
+            std::memcpy(&ih, ipc_handles + 64 * (size_t)q, 64);
+            void *m = nullptr;
+            CUDA_CHECK(cudaIpcOpenMemHandle(&m, ih, cudaIpcMemLazyEnablePeerAccess));
+            pr.region[q] = (uint8_t *)m;
+        }
+        pr.attached = true;
+        return 0;
+    });
+}
+int hmb200_peer_buffer(hmb200_handle *h, int index, void **ptr) {
+    if (!h || !ptr || index < 0 || index > 1 || !h->peer.region[h->peer.rank]) { g_last_error = "no peer region / bad index"; return 1; }
+    *ptr = h->peer.region[h->peer.rank] + (size_t)index * h->peer.buf_bytes;
+    return 0;
+}
+int hmb200_peer_status(hmb200_handle *h, int *err) {
+    return guarded([&] {
+        if (!h || !err || !h->peer.region[h->peer.rank]) throw std::runtime_error("no peer region");
+        CUDA_CHECK(cudaSetDevice(h->device));
+        CUDA_CHECK(cudaMemcpy(err, peer_ctrl_err(h->peer), sizeof(int), cudaMemcpyDeviceToHost));
+        return 0;
+    });
+}
+int hmb200_vector_product_allgather_d(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated) {
+    return guarded([&] { if (!h || h->es != 8) throw std::runtime_error("handle is not a real (double) engine"); return fused_product<double>(h, alpha, in, y_replicated); });
+}
+int hmb200_vector_product_allgather_z(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated) {
+    return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return fused_product<double2>(h, alpha, in, y_replicated); });
 }
 int hmb200_set_graphs(hmb200_handle *h, int on) {
     if (!h) { g_last_error = "null handle"; return 1; }

@@ -20,6 +20,8 @@
 
 namespace hmb200 {
 
+constexpr int kMaxPeers = 8;
+
 struct StreamParams {
     const uint8_t *stream;
     const StageEntry *stages;
@@ -33,6 +35,15 @@ struct StreamParams {
     const int32_t *out_perm; // optional fused cluster_to_user scatter: y[out_perm[row]] (perm already made local)
     double alpha_re, alpha_im, beta_re, beta_im;
     int stage_bytes, z_bytes, n_stages, consumer_warps;
+    // phase 2 only: the all-gather of the row slabs fused into the epilogue.  Every output row is also stored into the
+    // replicated vector of each peer GPU (peer-mapped memory over NVLink; pointers already offset to this rank's slab);
+    // when the whole grid is done the last CTA publishes this rank's epoch to every rank's flag word (release, system scope).
+    int n_peers;            // number of entries of peer_y (other ranks); 0 = plain product
+    int n_flags;            // number of entries of peer_flags (all ranks, own included); 0 = no signalling
+    void *peer_y[kMaxPeers];
+    unsigned long long *peer_flags[kMaxPeers]; // each points at the word "rank <me> finished epoch e" in that rank's flag block
+    unsigned long long *epoch;                 // this rank's product count for the buffer being written
+    uint32_t *done;                            // CTA completion counter (self-resetting)
 };
 
 constexpr int kBarrierBytes = 256;
@@ -286,11 +297,44 @@ __global__ void __launch_bounds__(17 * 32, 1) hmatrix_stream_kernel(const Stream
                 T r = S::mul(alpha, s);
                 if (!S::is_zero(beta)) r = S::add(r, S::mul(beta, y[o])); // beta == 0 must not propagate NaNs of y (BLAS)
                 y[o] = r;
+                for (int q = 0; q < p.n_peers; q++) reinterpret_cast<T *>(p.peer_y[q])[o] = r; // 512 B contiguous per bin and peer
             }
             acc0 = S::zero();
             acc1 = S::zero();
             bin_parity ^= 1;
         }
+    }
+    if (PHASE == 2 && p.n_flags > 0) {
+        // every thread that stored rows fences at system scope, the CTA counts itself done, and the last CTA of the grid
+        // publishes the new epoch to all ranks (the classic last-block pattern, extended to system scope)
+        __threadfence_system();
+        ptx::named_bar_sync(1, NW * 32);
+        if (threadIdx.x == 0) {
+            const uint32_t old = atomicAdd(p.done, 1u);
+            if (old == gridDim.x - 1) {
+                *p.done = 0;
+                const unsigned long long e = *p.epoch + 1ull;
+                *p.epoch = e;
+                __threadfence_system();
+                for (int q = 0; q < p.n_flags; q++) ptx::st_release_sys_u64(p.peer_flags[q], e);
+            }
+        }
+    }
+}
+
+// waits until every rank has published at least this rank's own epoch for the buffer (flags: n_ranks words in LOCAL memory
+// written by the peers' phase-2 kernels).  Bounded spin: after ~`max_cycles` clocks the error word is set and the kernel exits.
+__global__ void peer_wait_kernel(const unsigned long long *flags, int n_ranks, const unsigned long long *epoch, int *err, long long max_cycles) {
+    const int q = threadIdx.x;
+    if (q >= n_ranks) return;
+    const unsigned long long target = *epoch;
+    const long long t0 = clock64();
+    while (ptx::ld_acquire_sys_u64(flags + q) < target) {
+        if (clock64() - t0 > max_cycles) {
+            atomicExch(err, 1 + q);
+            break;
+        }
+        __nanosleep(200);
     }
 }
 

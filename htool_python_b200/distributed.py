@@ -60,6 +60,20 @@ def allgather_slabs_(buf, offs: List[int], sizes: List[int], mu: int, group=None
     return buf
 
 
+class _RawDeviceArray:
+    """`__cuda_array_interface__` view of device memory owned by libhmb200.so (wrapped by torch.as_tensor without a copy)"""
+
+    def __init__(self, ptr, n, is_complex):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<c16" if is_complex else "<f8", "data": (int(ptr), False), "version": 2, "strides": None}
+
+
+def _device_tensor(ptr, n, is_complex, device):
+    import torch
+
+    with torch.cuda.device(device):
+        return torch.as_tensor(_RawDeviceArray(ptr, n, is_complex), device=device)
+
+
 class B200DistributedOperator:
     """Drop-in for the product surface of `Htool.DistributedOperator` (`shape`, `*`, `@`;
     src/htool/distributed_operator/distributed_operator.hpp:16-65) backed by one `Engine` per rank.
@@ -74,7 +88,7 @@ class B200DistributedOperator:
         """single-process operator over an EXISTING engine (e.g. `B200HMatrix(...).engine`): nothing is packed or uploaded again"""
         return cls(flat, [(0, flat.n_rows)], group=group, device=engine.device, engine=engine)
 
-    def __init__(self, slab_flat, partition, group=None, device: Optional[int] = None, engine=None, **options):
+    def __init__(self, slab_flat, partition, group=None, device: Optional[int] = None, engine=None, fused_allgather=None, **options):
         import torch
         import torch.distributed as dist
 
@@ -103,6 +117,50 @@ class B200DistributedOperator:
         self.perm_s = torch.from_numpy(np.ascontiguousarray(slab_flat.source_permutation, np.int32)).to(self.device)
         self._x = {}  # mu -> (x_cluster, y_cluster) replicated device buffers
         self._pin = {}
+        self.fused = False
+        self._ybuf = None
+        if fused_allgather is None:
+            fused_allgather = self.world > 1
+        if fused_allgather:
+            self._setup_fused_allgather()
+
+    def _setup_fused_allgather(self):
+        """peer-mapped replicated output buffers (CUDA IPC over NVLink) for `matvec_cluster_fused_` (include/hmb200.h,
+        hmb200_peer_*).  Falls back to the NCCL all-gather with a warning when IPC mapping is not available."""
+        import ctypes
+        import warnings
+
+        import torch
+        import torch.distributed as dist
+
+        lib = _lib.lib()
+        handle = (ctypes.c_ubyte * 64)()
+        ok = lib.hmb200_peer_create(self.engine._h, self.world, self.rank, self.n_target, self.offs[self.rank], handle) == 0
+        err = "" if ok else _lib.last_error()
+        handles = [bytes(handle) if ok else None]
+        if self.world > 1:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle) if ok else None, group=self.group)
+        if ok and all(hd is not None for hd in handles):
+            blob = (ctypes.c_ubyte * (64 * self.world)).from_buffer_copy(b"".join(handles))
+            ok = lib.hmb200_peer_attach(self.engine._h, blob) == 0
+            err = "" if ok else _lib.last_error()
+        else:
+            ok = False
+        flags = [ok]
+        if self.world > 1:
+            flags = [None] * self.world
+            dist.all_gather_object(flags, ok, group=self.group)
+        if not all(flags):
+            warnings.warn(f"hmb200: fused all-gather unavailable ({err or 'a peer could not map the shared region'}); using NCCL")
+            return
+        bufs = []
+        for i in range(2):
+            ptr = ctypes.c_void_p()
+            _lib.check(lib.hmb200_peer_buffer(self.engine._h, i, ctypes.byref(ptr)))
+            bufs.append(_device_tensor(ptr.value, self.n_target, self.is_complex, self.device))
+        self._ybuf = {b.data_ptr(): b for b in bufs}
+        self.fused = True
 
     @property
     def shape(self):
@@ -111,9 +169,36 @@ class B200DistributedOperator:
     # ---- device-resident products in cluster numbering -------------------------------------------------------
     def matvec_cluster_(self, x_cluster, y_cluster):
         """y_cluster (replicated, length n_target) = A x_cluster; both CUDA tensors; slab product + all-gather."""
+        if self.fused:
+            y_cluster.copy_(self.matvec_cluster_fused_(x_cluster))
+            return y_cluster
         o, s = self.offs[self.rank], self.sizes[self.rank]
         self.engine.add_vector_product("N", 1.0, x_cluster, 0.0, y_cluster[o:o + s])
         return allgather_slabs_(y_cluster, self.offs, self.sizes, 1, self.group)
+
+    def matvec_cluster_fused_(self, x_cluster):
+        """returns the replicated y = A x (cluster numbering) as a view of one of the operator's two peer-mapped buffers: the
+        slab product stores its rows into every rank's buffer from the phase-2 epilogue (no NCCL call).  Collective; the
+        returned tensor stays valid until the product after the next one."""
+        import ctypes
+
+        if not self.fused:
+            raise RuntimeError("fused all-gather is not set up on this operator")
+        eng = self.engine
+        px, _ = eng._ptr(x_cluster, self.n_source, False)
+        out = ctypes.c_void_p()
+        one = (ctypes.c_double * 2)(1.0, 0.0)
+        fn = _lib.lib().hmb200_vector_product_allgather_z if self.is_complex else _lib.lib().hmb200_vector_product_allgather_d
+        _lib.check(fn(eng._h, one, px, ctypes.byref(out)))
+        return self._ybuf[out.value]
+
+    def peer_status(self) -> int:
+        """0, or 1 + the rank whose epoch did not arrive within the wait kernel's bound (synchronises)"""
+        import ctypes
+
+        err = ctypes.c_int(0)
+        _lib.check(_lib.lib().hmb200_peer_status(self.engine._h, ctypes.byref(err)))
+        return err.value
 
     def matmat_cluster_(self, X_cluster, Y_cluster, mu: int):
         """row-major (n x mu) blocks (add_distributed_operator_matrix_product_row_major_global_to_global.hpp:18-84)."""
@@ -174,7 +259,7 @@ class B200DistributedOperator:
                 src = pin_x
             xu.copy_(src, non_blocking=True)
             self._permute(True, self.perm_s, self.n_source, xu, xc, 1)     # global_to_root_cluster (:108)
-            self.matvec_cluster_(xc, yc)
+            yc = self.matvec_cluster_fused_(xc) if self.fused else self.matvec_cluster_(xc, yc)
             self._permute(False, self.perm_t, self.n_target, yc, yu, 1)    # root_cluster_to_global (:117)
             dst = self._as_pinned_tensor(out) if out is not None else None
             (dst if dst is not None else pin_y).copy_(yu, non_blocking=True)

@@ -129,6 +129,24 @@ int hmb200_set_cluster_offsets(hmb200_handle *h, int target_offset, int source_o
 int hmb200_add_sub_matrix_product_to_local_d(hmb200_handle *h, const double *in, double *out, int mu, int offset, int size, int mem);
 int hmb200_add_sub_matrix_product_to_local_z(hmb200_handle *h, const double *in, double *out, int mu, int offset, int size, int mem);
 
+/* ---- block-row product with the all-gather fused into the kernel (one process per GPU, GPUs of one node) -------------
+ * Replaces the slab product + MPI_Allgatherv of add_distributed_operator_vector_product_global_to_global
+ *   (core/distributed_operator/linalg/add_distributed_operator_vector_product_global_to_global.hpp:63-76): the phase-2
+ *   epilogue stores every output row of this rank's slab into the replicated vector of EVERY rank through peer-mapped
+ *   memory (CUDA IPC over NVLink), the last CTA publishes an epoch flag to all ranks, and a one-warp kernel waits for the
+ *   epochs of all ranks.  No NCCL call, no host synchronisation; two replicated buffers alternate.
+ *   1. every rank: hmb200_peer_create(h, n_ranks, rank, n_global, slab_offset, handle[64]) -- allocates its shared region
+ *   2. exchange the 64-byte handles (any transport), then hmb200_peer_attach(h, handles: n_ranks x 64 bytes in rank order)
+ *   3. collectively, the same number of times on every rank: hmb200_vector_product_allgather_{d,z}(h, alpha, in, &y):
+ *      y (device pointer into this rank's region, n_global elements, cluster numbering) = alpha * A * in on all ranks;
+ *      asynchronous on the handle's stream.  hmb200_peer_status reads the error word (non-zero: a peer did not arrive). */
+int hmb200_peer_create(hmb200_handle *h, int n_ranks, int rank, int64_t n_global, int slab_offset, unsigned char *ipc_handle_out);
+int hmb200_peer_attach(hmb200_handle *h, const unsigned char *ipc_handles);
+int hmb200_peer_buffer(hmb200_handle *h, int index, void **ptr);
+int hmb200_peer_status(hmb200_handle *h, int *err);
+int hmb200_vector_product_allgather_d(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated);
+int hmb200_vector_product_allgather_z(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated);
+
 /* ---- permutations (bit-exact) -----------------------------------------------------------------------------------
  * gather : out[i] = in[perm[off+i]-off]   user_to_cluster / global_to_root_cluster (core/clustering/cluster_node.hpp:110-119,162-175)
  * scatter: out[perm[off+i]-off] = in[i]   cluster_to_user / root_cluster_to_global (core/clustering/cluster_node.hpp:99-109,149-161)

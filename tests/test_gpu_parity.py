@@ -254,7 +254,35 @@ def _dist_worker(rank, world, port, q):
         y_ref, Y_ref = np.empty(n), np.empty((n, mu))
         y_ref[slab.target_permutation] = yb
         Y_ref[slab.target_permutation] = Yb
-        q.put((rank, rel_err(y, y_ref), rel_err(Y, Y_ref), bool(Y.flags.f_contiguous)))
+        # the all-gather fused into the phase-2 epilogue (peer stores over NVLink): repeated products alternate the two
+        # replicated buffers and are replayed from CUDA graphs; bit-identical to each other and to the NCCL all-gather path
+        ys = [op * x for _ in range(6)]
+        same = all(np.array_equal(v, y) for v in ys)
+        op_nccl = B200DistributedOperator(slab, tree.partition, fused_allgather=False)
+        same = same and np.array_equal(op_nccl * x, y) and not op_nccl.fused
+        status = op.peer_status() if op.fused else 0
+        # device GMRES on the distributed operator vs the oracle GMRES over the restated slabs
+        from htool_python_b200 import B200Solver
+        from oracle import gmres_oracle as go
+
+        flats = [FlatHMatrix.from_htool(Hp if p == rank else bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-4, eta=10.0, target_partition_number=p, partition_number_for_symmetry=p)) for p in range(world)]
+
+        def matvec(v):
+            vc = np.ascontiguousarray(v[slab.source_permutation])
+            yc = np.zeros(n)
+            for p, f in enumerate(flats):
+                fo.add_vector_product(f, "N", 1.0, vc, 0.0, yc[offs[p]:offs[p] + sizes[p]])
+            out = np.empty(n)
+            out[slab.target_permutation] = yc
+            return out
+
+        args = "-hpddm_krylov_method gmres -hpddm_schwarz_method none -hpddm_tol 1e-8 -hpddm_gmres_restart 20 -hpddm_max_it 100 -hpddm_variant right"
+        b = helpers.rand_vec(rng, n, np.float64)
+        xs = np.zeros(n)
+        it = B200Solver(op).solve(xs, b, args)
+        x_ref, it_ref, _ = go.gmres(matvec, b, **go.parse_hpddm_args(args))
+        q.put((rank, rel_err(y, y_ref), rel_err(Y, Y_ref), bool(Y.flags.f_contiguous), bool(op.fused), same, status, it, it_ref, rel_err(xs, x_ref)))
+        op_nccl.close()
         op.close()
     finally:
         dist.destroy_process_group()
@@ -283,8 +311,11 @@ def test_distributed_operator(world):
     res = [q.get(timeout=300) for _ in range(world)]
     for p in procs:
         p.join(timeout=120)
-    for rank, e1, e2, f_order in res:
+    for rank, e1, e2, f_order, fused, same, status, it, it_ref, ex in res:
         assert e1 < TOL and e2 < TOL and f_order, (rank, e1, e2)
+        assert same and status == 0, (rank, same, status)
+        assert fused == (world > 1), "the fused all-gather must be the path that runs on several GPUs"
+        assert it == it_ref and 0 < it < 100 and ex < 1e-7, (rank, it, it_ref, ex)
 
 
 @pytest.mark.parametrize("name,mu", [("d_N_cylinder", 64), ("d_N_rect", 70), ("d_SL_cylinder", 17), ("z_N_sphere", 32), ("z_HL_cylinder", 40), ("z_SL_sphere", 5)])
@@ -414,9 +445,33 @@ def test_device_products_replayed_from_cuda_graphs():
         r = y0.cpu().numpy().copy()
         fo.add_vector_product(flat, "N", a, xv.cpu().numpy(), b, r)
         assert rel_err(y.cpu().numpy(), r) < TOL
-    _lib_check = __import__("htool_python_b200")._lib
-    _lib_check.check(_lib_check.lib().hmb200_set_graphs(e._h, 0))
+    from htool_python_b200 import _lib
+
+    _lib.check(_lib.lib().hmb200_set_graphs(e._h, 0))
     y.copy_(y0)
     e.add_vector_product("N", 1.5, x, -0.25, y)
     assert np.array_equal(y.cpu().numpy(), outs[0])
     e.close()
+
+
+def test_fused_allgather_protocol_single_rank():
+    """the peer-store epilogue + epoch flags + wait kernel with one rank (its own flag only): buffers alternate, graphs replay"""
+    import torch
+
+    from htool_python_b200 import B200DistributedOperator
+
+    flat, z = load_golden("d_N_cylinder")
+    op = B200DistributedOperator(flat, [(0, flat.n_rows)], fused_allgather=True)
+    assert op.fused
+    xc = torch.from_numpy(np.ascontiguousarray(z["x"][flat.source_permutation])).cuda()
+    y_ref = np.zeros(flat.n_rows)
+    fo.add_vector_product(flat, "N", 1.0, xc.cpu().numpy(), 0.0, y_ref)
+    ptrs = []
+    for k in range(7):
+        yk = op.matvec_cluster_fused_(xc)
+        ptrs.append(yk.data_ptr())
+        assert rel_err(yk.cpu().numpy(), y_ref) < TOL, k
+    assert ptrs[0] != ptrs[1] and ptrs[0::2] == [ptrs[0]] * 4 and ptrs[1::2] == [ptrs[1]] * 3
+    assert op.peer_status() == 0
+    assert rel_err(op * z["x"], z["y_ref"]) < TOL
+    op.close()
