@@ -105,6 +105,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.stop_flag, self.sm, self.reasons, self.sm_max = index, False, [], set(), None
+        self.t, self.window = [], None  # sample times; (t0, t1) of the timed region
         try:
             import pynvml
 
@@ -125,19 +126,24 @@ class ClockSampler(threading.Thread):
         while not self.stop_flag:
             try:
                 self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                self.t.append(time.perf_counter())
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
                 for bit, name in names.items():
                     if r & bit:
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.004)
 
     def result(self):
         self.stop_flag = True
         if self.nv is None or not self.sm:
             return {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": []}
-        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons)}
+        sm = self.sm
+        if self.window:  # samples inside the timed region; a region shorter than the sampling period falls back to all samples
+            inside = [v for v, t in zip(self.sm, self.t) if self.window[0] <= t <= self.window[1]]  # (the thread runs from the warm-up on)
+            sm = inside or sm
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons), "samples": len(sm)}
 
 
 def w_split(flat):
@@ -180,7 +186,7 @@ def run_b200(args):
     opts = {k: int(v) for k, v in (kv.split("=") for kv in args.engine_opts.split(",") if kv)}
     t0 = time.time()
     if world > 1:
-        op = B200DistributedOperator(flat, tree.partition, device=local_rank, **opts)
+        op = B200DistributedOperator(flat, tree.partition, device=local_rank, fused_allgather=False if os.environ.get("HMB200_NO_FUSED") else None, **opts)
         engine = op.engine
     else:
         op = B200HMatrix(flat, device=local_rank, **opts)
@@ -228,18 +234,23 @@ def run_b200(args):
         apply_user = lambda: op.matvec(x_pin, out=y_pin)  # noqa: E731
 
     # ---- device-resident timed region ------------------------------------------------------------------------
+    # NVML is initialised and the sampling thread started BEFORE the region (nvmlInit takes a rank-dependent time: inside the
+    # barrier-to-event window it skews the ranks and the skew lands in the first step's wait); only rank 0 samples its GPU
+    sampler = ClockSampler(local_rank)
+    if rank == 0 and not os.environ.get("HMB200_BENCH_NO_SAMPLER"):
+        sampler.start()
     for _ in range(args.warmup):
         step()
     barrier()
     launches0 = engine.launch_count
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_region = time.perf_counter()
     ev0.record()
     for _ in range(args.steps):
         step()
     ev1.record()
     barrier()
+    sampler.window = (t_region, time.perf_counter())
     clocks = sampler.result()
     ms_total = ev0.elapsed_time(ev1)
     launches = engine.launch_count - launches0
