@@ -287,17 +287,26 @@ __global__ void __launch_bounds__(17 * 32, 1) hmatrix_stream_kernel(const Stream
             red[warp * kMaxBinRows + lane]      = acc0;
             red[warp * kMaxBinRows + 32 + lane] = acc1;
             ptx::named_bar_sync(1, NW * 32);
-            const uint32_t tid = threadIdx.x;
-            if (tid < bin_rows) {
-                T s = red[tid];
-                for (int w = 1; w < NW; w++) s = S::add(s, red[w * kMaxBinRows + tid]);
-                const T alpha = S::make(p.alpha_re, p.alpha_im), beta = S::make(p.beta_re, p.beta_im);
-                T *y = (T *)p.y;
-                const size_t o = p.out_perm ? (size_t)p.out_perm[row0 + tid] : (size_t)(row0 + tid);
+            // every (target, row) pair is taken by one consumer thread: target 0 is this rank's y, targets 1.. are the peers'
+            // replicated vectors (fused all-gather).  With 16 consumer warps and 7 peers each thread issues exactly one store, so
+            // the remote stores of a bin leave in parallel instead of trailing behind two warps.  All targets get the same bits
+            // (same summation order).
+            const T alpha = S::make(p.alpha_re, p.alpha_im), beta = S::make(p.beta_re, p.beta_im);
+            const uint32_t n_items = (uint32_t)(1 + p.n_peers) * kMaxBinRows;
+            for (uint32_t idx = threadIdx.x; idx < n_items; idx += (uint32_t)NW * 32u) {
+                const uint32_t r_ = idx % kMaxBinRows, tgt = idx / kMaxBinRows;
+                if (r_ >= bin_rows) continue;
+                T s = red[r_];
+                for (int w = 1; w < NW; w++) s = S::add(s, red[w * kMaxBinRows + r_]);
                 T r = S::mul(alpha, s);
-                if (!S::is_zero(beta)) r = S::add(r, S::mul(beta, y[o])); // beta == 0 must not propagate NaNs of y (BLAS)
-                y[o] = r;
-                for (int q = 0; q < p.n_peers; q++) reinterpret_cast<T *>(p.peer_y[q])[o] = r; // 512 B contiguous per bin and peer
+                if (tgt == 0) {
+                    T *y = (T *)p.y;
+                    const size_t o = p.out_perm ? (size_t)p.out_perm[row0 + r_] : (size_t)(row0 + r_);
+                    if (!S::is_zero(beta)) r = S::add(r, S::mul(beta, y[o])); // beta == 0 must not propagate NaNs of y (BLAS)
+                    y[o] = r;
+                } else {
+                    reinterpret_cast<T *>(p.peer_y[tgt - 1])[row0 + r_] = r; // beta = 0, cluster numbering (fused path)
+                }
             }
             acc0 = S::zero();
             acc1 = S::zero();
