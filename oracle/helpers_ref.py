@@ -60,6 +60,9 @@ def hpddm_solve(matvec, b, x0=None, args="", mu=1):
         calls[0] += 1
         return 0
 
+    # '-hpddm_schwarz_method' is registered by htool's DDM wrapper, not by HPDDM itself (it would only print a warning on stdout)
+    toks = args.split()
+    args = " ".join(t for i, t in enumerate(toks) if t != "-hpddm_schwarz_method" and not (i > 0 and toks[i - 1] == "-hpddm_schwarz_method"))
     fn = lib.hpddm_ref_solve_z if cplx else lib.hpddm_ref_solve_d
     fn.restype = ctypes.c_int
     it = fn(ctypes.c_int(n), CB(cb), None, ctypes.c_void_p(bf.ctypes.data), ctypes.c_void_p(x.ctypes.data), ctypes.c_int(mu), args.encode())
