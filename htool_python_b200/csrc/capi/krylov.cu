@@ -36,7 +36,7 @@ void check_common(int64_t n, int elem_bytes) {
 
 template <typename T>
 void reduce_partials(const T *partial, int chunks, int k, T *out, cudaStream_t s) {
-    krylov_reduce_kernel<T><<<(k + 127) / 128, 128, 0, s>>>(partial, chunks, k, out);
+    krylov_reduce_kernel<T><<<(k + 7) / 8, 256, 0, s>>>(partial, chunks, k, out); // one warp per j
 }
 
 template <typename T>

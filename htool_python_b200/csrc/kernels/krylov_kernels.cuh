@@ -95,14 +95,23 @@ __global__ void __launch_bounds__(kKrylovThreads) krylov_dots_kernel(const T *__
     }
 }
 
-// out[j] = sum_c partial[c * k + j], c ascending (one thread per j; the partials are a few hundred entries per j)
+// out[j] = sum_c partial[c * k + j]: one warp per j, lane l sums the chunks l, l+32, ... in ascending order, then a fixed
+// xor-shuffle tree (deterministic; the partials are a few hundred entries per j, so this is pure latency: 1 dependent load
+// chain of n_chunks/32 instead of n_chunks)
 template <typename T>
-__global__ void krylov_reduce_kernel(const T *__restrict__ partial, int n_chunks, int k, T *__restrict__ out) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256) krylov_reduce_kernel(const T *__restrict__ partial, int n_chunks, int k, T *__restrict__ out) {
+    const int j = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
     if (j >= k) return;
-    T acc = Scalar<T>::zero();
-    for (int c = 0; c < n_chunks; c++) acc = Scalar<T>::add(acc, partial[(int64_t)c * k + j]);
-    out[j] = acc;
+    T a0 = Scalar<T>::zero(), a1 = a0;
+    int c = lane;
+    for (; c + 32 < n_chunks; c += 64) {
+        const T p0 = partial[(int64_t)c * k + j], p1 = partial[(int64_t)(c + 32) * k + j];
+        a0 = Scalar<T>::add(a0, p0);
+        a1 = Scalar<T>::add(a1, p1);
+    }
+    if (c < n_chunks) a0 = Scalar<T>::add(a0, partial[(int64_t)c * k + j]);
+    const T acc = warp_sum<T>(Scalar<T>::add(a0, a1));
+    if (lane == 0) out[j] = acc;
 }
 
 // w[row] += sign * sum_j h[j] * V[j][row]; optional ||w||^2 partial per CTA

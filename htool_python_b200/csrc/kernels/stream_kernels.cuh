@@ -356,17 +356,24 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const ReduceSeg *s
     if (w >= n_segs) return;
     const uint4 sg = __ldg(reinterpret_cast<const uint4 *>(segs + w));
     const int len = (int)sg.w, G = 32 / len, l = lane % len, g = lane / len;
-    T s0 = S::zero(), s1 = S::zero();
+    // latency-bound (a segment of a wide V tile has > 100 partials): 8 independent loads in flight per lane, fixed order
+    T s0 = S::zero(), s1 = S::zero(), s2 = S::zero(), s3 = S::zero();
     if (g < G) {
         const T *pp = xz + sg.y + l;
+        const size_t st = (size_t)G * len;
         uint32_t q = g;
-        for (; q + G < sg.z; q += 2 * G) {
-            s0 = S::add(s0, pp[(size_t)q * len]);
-            s1 = S::add(s1, pp[(size_t)(q + G) * len]);
+        const T *pq = pp + (size_t)q * len;
+        for (; q + 7 * G < sg.z; q += 8 * G, pq += 8 * st) {
+            const T a0 = pq[0], a1 = pq[st], a2 = pq[2 * st], a3 = pq[3 * st];
+            const T a4 = pq[4 * st], a5 = pq[5 * st], a6 = pq[6 * st], a7 = pq[7 * st];
+            s0 = S::add(S::add(s0, a0), a4);
+            s1 = S::add(S::add(s1, a1), a5);
+            s2 = S::add(S::add(s2, a2), a6);
+            s3 = S::add(S::add(s3, a3), a7);
         }
-        if (q < sg.z) s0 = S::add(s0, pp[(size_t)q * len]);
+        for (; q < sg.z; q += G, pq += st) s0 = S::add(s0, pq[0]);
     }
-    s0 = S::add(s0, s1);
+    s0 = S::add(S::add(s0, s1), S::add(s2, s3));
     for (int gg = 1; gg < G; gg++) {
         const T o = S::shfl(s0, lane < len ? lane + gg * len : lane);
         if (lane < len) s0 = S::add(s0, o);

@@ -111,7 +111,10 @@ def gmres_driver(sp, b_host, x_host, opt: dict):
         norm_b = 1.0
     V = sp.basis(m + 1)
     hess = _Hessenberg(m, sp.np_dtype)
-    calls, residuals = 0, []
+    calls, residuals, unused = 0, [], 0
+    speculate = bool(opt.get("speculate", True)) and hasattr(sp, "host_begin")
+    if not hasattr(sp, "host_begin"):  # spaces without an asynchronous read: read synchronously
+        sp.host_begin, sp.host_end = (lambda handles: handles), (lambda token: sp.host(token))
     conv = -m
     j = 1
     while j <= max_it:
@@ -127,9 +130,12 @@ def gmres_driver(sp, b_host, x_host, opt: dict):
         hess.start(math.sqrt(beta2))
         sp.scale(V.row(0), beta2_dev)
         i = 0
+        launched = False  # the product of step i was already enqueued (speculatively) by step i-1
         while i < m and j <= max_it:
             w = V.row(i + 1)
-            sp.matvec(V.row(i), w)
+            if not launched:
+                sp.matvec(V.row(i), w)
+            launched = False
             calls += 1
             if mgs:  # HPDDM_iterative.hpp:522-540
                 hs = []
@@ -138,15 +144,24 @@ def gmres_driver(sp, b_host, x_host, opt: dict):
                     hk = sp.dots(V, k, 1, w)
                     n2_dev = sp.combine(V, k, 1, hk, -1.0, w, want_norm=(k == i))
                     hs.append(hk)
-                got = sp.host(hs + [n2_dev])
-                hcol, n2 = np.array([g[0] for g in got[:-1]]), float(got[-1].real.reshape(-1)[0])
+                token = sp.host_begin(hs + [n2_dev])
             else:  # classical Gram-Schmidt (:541-552)
                 h_dev = sp.dots(V, 0, i + 1, w)
                 n2_dev = sp.combine(V, 0, i + 1, h_dev, -1.0, w, want_norm=True)
-                got = sp.host([h_dev, n2_dev])
-                hcol, n2 = got[0], float(got[1].real.reshape(-1)[0])
+                token = sp.host_begin([h_dev, n2_dev])
             if i < m - 1:
                 sp.scale(w, n2_dev)
+                if speculate and j + 1 <= max_it:
+                    # enqueue the NEXT operator call before the host reads the Hessenberg column: the device computes it
+                    # while the host does the Givens update and the convergence test.  If this step converges the product
+                    # is simply unused (counted in info["speculative_unused"], not in operator_calls).
+                    sp.matvec(w, V.row(i + 2))
+                    launched = True
+            got = sp.host_end(token)
+            if mgs:
+                hcol, n2 = np.array([g[0] for g in got[:-1]]), float(got[-1].real.reshape(-1)[0])
+            else:
+                hcol, n2 = got[0], float(got[1].real.reshape(-1)[0])
             res = hess.push(i, hcol, n2)
             i += 1
             residuals.append(res / norm_b)
@@ -154,6 +169,7 @@ def gmres_driver(sp, b_host, x_host, opt: dict):
                 conv = i
             if conv != -m:
                 i = 0
+                unused += int(launched)
                 break
             j += 1
         if j != max_it + 1 and i == m:  # restart
@@ -168,7 +184,7 @@ def gmres_driver(sp, b_host, x_host, opt: dict):
         sp.combine(V, 0, abs(conv), sp.upload(hess.solve(abs(conv))), 1.0, x, want_norm=False)
     it = min(j, max_it)
     x_out = sp.get_to_user(x)
-    return x_out, it, dict(operator_calls=calls, residuals=residuals, converged=bool(j <= max_it), norm_b=norm_b)
+    return x_out, it, dict(operator_calls=calls, residuals=residuals, converged=bool(j <= max_it), norm_b=norm_b, speculative_unused=unused)
 
 
 class _Basis:
@@ -202,6 +218,7 @@ class CudaKrylovSpace:
         self._xu = torch.empty(self.n_global, dtype=self.dtype, device=self.device)   # user-numbering staging
         self._pin = torch.empty(self.n_global, dtype=self.dtype).pin_memory()
         self._scratch = None
+        self._hpin, self._hev = None, None
         self._k_max = 0
         self.kernel_launches = 0
 
@@ -316,6 +333,31 @@ class CudaKrylovSpace:
             else:
                 out.append(vals[p:p + h.numel()].copy())
                 p += h.numel()
+        return out
+
+    def host_begin(self, handles):
+        """enqueues the device->host copy of a few scalars into page-locked memory and records an event; `host_end` waits for
+        that event only, so kernels enqueued in between (the speculative next product) keep the device busy"""
+        torch = self.torch
+        flat = torch.cat([torch.view_as_real(h).reshape(-1) if h.is_complex() else h.reshape(-1).to(torch.float64) for h in handles])
+        if self._hpin is None or self._hpin.numel() < flat.numel():
+            self._hpin = torch.empty(max(2 * flat.numel(), 1024), dtype=torch.float64).pin_memory()
+            self._hev = torch.cuda.Event()
+        self._hpin[:flat.numel()].copy_(flat, non_blocking=True)
+        self._hev.record(torch.cuda.current_stream(self.device))
+        return [(h.is_complex(), h.numel()) for h in handles]
+
+    def host_end(self, token):
+        self._hev.synchronize()
+        vals = self._hpin.numpy()
+        out, p = [], 0
+        for is_c, n in token:
+            if is_c:
+                out.append(vals[p:p + 2 * n].view(np.complex128).copy())
+                p += 2 * n
+            else:
+                out.append(vals[p:p + n].copy())
+                p += n
         return out
 
     def upload(self, y):

@@ -1,0 +1,33 @@
+"""One device-resident GMRES cycle on the N-point Laplace operator (for ncu launch lists / captures of the Krylov kernels)."""
+import os
+import sys
+import time
+import types
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+from htool_python_b200 import B200DistributedOperator, B200HMatrix, B200Solver  # noqa: E402
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
+max_it = int(sys.argv[2]) if len(sys.argv) > 2 else 45
+args = types.SimpleNamespace(n=n, eps=1e-3, eta=10.0, leaf=64, kernel="laplace", wavenumber=0.0)
+torch.cuda.set_device(0)
+tree, H, flat, bt = bench.assemble(args, 1, 0, lambda m: print("[gmres-profile]", m, file=sys.stderr, flush=True))
+hb = B200HMatrix(flat, device=0)
+op = B200DistributedOperator.from_engine(hb.engine, flat)
+solver = B200Solver(op)
+b = op.matvec(np.random.default_rng(3).random(n))
+x = np.zeros(n)
+opts = f"-hpddm_krylov_method gmres -hpddm_schwarz_method none -hpddm_tol 1e-12 -hpddm_gmres_restart 40 -hpddm_max_it {max_it}"
+solver.solve(x, b, opts)
+x[:] = 0
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+it = solver.solve(x, b, opts)
+torch.cuda.synchronize()
+dt = time.perf_counter() - t0
+print(f"gmres-profile: n={n} iterations={it} solve {dt * 1e3:.2f} ms = {dt * 1e3 / it:.3f} ms/iteration, kernel launches (krylov/permute) {solver.space.kernel_launches}")

@@ -81,5 +81,11 @@ class NumpyKrylovSpace:
     def host(self, handles):
         return [np.array(h) for h in handles]
 
+    def host_begin(self, handles):  # snapshot now (the device version copies at this point of the stream)
+        return [np.array(h) for h in handles]
+
+    def host_end(self, token):
+        return token
+
     def upload(self, y):
         return np.asarray(y, dtype=self.np_dtype)
