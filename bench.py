@@ -56,6 +56,12 @@ def parse():
     return ap.parse_args()
 
 
+def workload_name(args, n, mu):
+    cfg = (1 if mu == 1 else 3) if args.kernel == "laplace" else 2
+    return (f"{WORKLOADS[args.kernel]} H-matrix, N={n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
+            f"leaf {args.leaf}, {'single-RHS matvec' if mu == 1 else str(mu) + '-RHS matmat (DMMA path)'} (BASELINE.json configs[{cfg}])")
+
+
 def sphere_points(n, seed=0):
     """N points uniformly on the unit sphere surface (normalised Gaussian, seed 0) -- SURVEY.md 8(d) C2."""
     g = np.random.default_rng(seed).standard_normal((3, n))
@@ -335,8 +341,7 @@ def run_b200(args):
             "metric": METRIC, "value": round(mu * 1e3 / ms_step, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if flat.dtype == "d" else "c128",
             "data": "synthetic",
-            "config": {"workload": f"{WORKLOADS[args.kernel]} H-matrix, N={n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
-                                   f"leaf {args.leaf}, {'single-RHS matvec' if mu == 1 else str(mu) + '-RHS matmat (DMMA path)'} (BASELINE.json configs[{(1 if mu == 1 else 3) if args.kernel == 'laplace' else 2}])",
+            "config": {"workload": workload_name(args, n, mu),
                        "rhs_per_step": mu, "partition": f"block-row slabs x{world}",
                        "allgather": ("none (1 GPU)" if world == 1 else "fused into the phase-2 epilogue: peer stores over NVLink + epoch flags (CUDA IPC)" if (mu == 1 and op.fused) else "NCCL all-gather"),
                        "launch": "CUDA graph replay of the product (captured by libhmb200.so)" if mu == 1 else "eager", "l2": "inputs larger than L2 (factor stream >> 126 MB, read once per step)",
@@ -469,8 +474,7 @@ def run_reference(args):
     v = round(max(1, args.rhs) / dt, 4)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(dt * 1e3, 3), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"Laplace 1/(4 pi r) H-matrix, N={args.n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
-                                   f"leaf {args.leaf}, double, single-RHS matvec (BASELINE.json configs[1])", **build_t},
+            "config": {"workload": workload_name(args, args.n, mu), "rhs_per_step": mu, **build_t},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": thr, "kind": "reference",
                              "sample": "each step = one full matvec, reference add_hmatrix_vector_product(exec_compat::par) from oracle/_ref"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}

@@ -484,6 +484,14 @@ void run_cached(hmb200_handle *h, const hmb200_handle::GraphKey &key, F &&issue)
         issue();
         return;
     }
+    {   // the caller is capturing h->stream into a graph of its own (e.g. torch.cuda.graph): record the plain sequence there
+        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(h->stream, &st) != cudaSuccess) { cudaGetLastError(); st = cudaStreamCaptureStatusActive; }
+        if (st != cudaStreamCaptureStatusNone) {
+            issue();
+            return;
+        }
+    }
     if (h->graphs.size() > 256) clear_graphs(h);
     auto &ge = h->graphs[key];
     if (!ge.exec && ++ge.seen < 2 && key.fused == 0) {

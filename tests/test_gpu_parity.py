@@ -213,7 +213,7 @@ def test_native_assembled_hmatrices(kernel, sym, uplo, n, leaf):
     e.close()
 
 
-def _dist_worker(rank, world, port, q):
+def _dist_worker(rank, world, port, q, kernel="laplace_reg"):
     import os
 
     import torch
@@ -230,28 +230,29 @@ def _dist_worker(rank, world, port, q):
         g = rng.standard_normal((3, n))
         pts = np.asfortranarray(g / np.linalg.norm(g, axis=0))
         tree = bridge.create_cluster_tree(pts, 2, world, 32)
-        Hp = bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-4, eta=10.0, target_partition_number=rank, partition_number_for_symmetry=rank)
+        build = lambda p: bridge.build_hmatrix(kernel, tree, epsilon=1e-4, eta=10.0, target_partition_number=p, partition_number_for_symmetry=p, wavenumber=3.0)  # noqa: E731
+        Hp = build(rank)
         slab = FlatHMatrix.from_htool(Hp)
+        dt = slab.np_dtype
         op = B200DistributedOperator(slab, tree.partition)
-        x = helpers.rand_vec(rng, n, np.float64)
-        X = np.asfortranarray(helpers.rand_vec(rng, n, np.float64, mu))
+        x = helpers.rand_vec(rng, n, dt)
+        X = np.asfortranarray(helpers.rand_vec(rng, n, dt, mu))
         y = op * x
         Y = op @ X
         # oracle: every slab's product (each rank restates ALL slabs on the CPU), assembled as the reference driver does
         offs, sizes = op.offs, op.sizes
-        yb = np.zeros(n)
-        Yb = np.zeros((n, mu))
-        xb, Xb = x[slab.source_permutation], np.ascontiguousarray(X[slab.source_permutation])
-        for p in range(world):
-            Hq = Hp if p == rank else bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-4, eta=10.0, target_partition_number=p, partition_number_for_symmetry=p)
-            fq = FlatHMatrix.from_htool(Hq)
-            out = np.zeros(sizes[p])
+        yb = np.zeros(n, dt)
+        Yb = np.zeros((n, mu), dt)
+        xb, Xb = np.ascontiguousarray(x[slab.source_permutation]), np.ascontiguousarray(X[slab.source_permutation])
+        flats = [FlatHMatrix.from_htool(Hp if p == rank else build(p)) for p in range(world)]
+        for p, fq in enumerate(flats):
+            out = np.zeros(sizes[p], dt)
             fo.add_vector_product(fq, "N", 1.0, xb, 0.0, out)
             yb[offs[p]:offs[p] + sizes[p]] = out
-            outm = np.zeros((sizes[p], mu))
+            outm = np.zeros((sizes[p], mu), dt)
             fo.add_matrix_product_row_major(fq, "N", 1.0, Xb, 0.0, outm, mu)
             Yb[offs[p]:offs[p] + sizes[p]] = outm
-        y_ref, Y_ref = np.empty(n), np.empty((n, mu))
+        y_ref, Y_ref = np.empty(n, dt), np.empty((n, mu), dt)
         y_ref[slab.target_permutation] = yb
         Y_ref[slab.target_permutation] = Yb
         # the all-gather fused into the phase-2 epilogue (peer stores over NVLink): repeated products alternate the two
@@ -265,20 +266,18 @@ def _dist_worker(rank, world, port, q):
         from htool_python_b200 import B200Solver
         from oracle import gmres_oracle as go
 
-        flats = [FlatHMatrix.from_htool(Hp if p == rank else bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-4, eta=10.0, target_partition_number=p, partition_number_for_symmetry=p)) for p in range(world)]
-
         def matvec(v):
             vc = np.ascontiguousarray(v[slab.source_permutation])
-            yc = np.zeros(n)
+            yc = np.zeros(n, dt)
             for p, f in enumerate(flats):
                 fo.add_vector_product(f, "N", 1.0, vc, 0.0, yc[offs[p]:offs[p] + sizes[p]])
-            out = np.empty(n)
+            out = np.empty(n, dt)
             out[slab.target_permutation] = yc
             return out
 
         args = "-hpddm_krylov_method gmres -hpddm_schwarz_method none -hpddm_tol 1e-8 -hpddm_gmres_restart 20 -hpddm_max_it 100 -hpddm_variant right"
-        b = helpers.rand_vec(rng, n, np.float64)
-        xs = np.zeros(n)
+        b = helpers.rand_vec(rng, n, dt)
+        xs = np.zeros(n, dt)
         it = B200Solver(op).solve(xs, b, args)
         x_ref, it_ref, _ = go.gmres(matvec, b, **go.parse_hpddm_args(args))
         q.put((rank, rel_err(y, y_ref), rel_err(Y, Y_ref), bool(Y.flags.f_contiguous), bool(op.fused), same, status, it, it_ref, rel_err(xs, x_ref)))
@@ -289,8 +288,9 @@ def _dist_worker(rank, world, port, q):
 
 
 @pytest.mark.skipif(not helpers.bridge_available(), reason="bridge not built")
+@pytest.mark.parametrize("kernel", ["laplace_reg", "complex_reg"])
 @pytest.mark.parametrize("world", [1, 2])
-def test_distributed_operator(world):
+def test_distributed_operator(world, kernel):
     """B200DistributedOperator `*` / `@` (user numbering, host arrays) vs the restated block-row driver on the oracle."""
     import socket
 
@@ -305,7 +305,7 @@ def test_distributed_operator(world):
     s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_dist_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_dist_worker, args=(r, world, port, q, kernel)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=300) for _ in range(world)]
