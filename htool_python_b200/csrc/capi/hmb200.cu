@@ -4,6 +4,7 @@
 #include "planner.h"
 #include "../kernels/stream_kernels.cuh"
 #include "../kernels/mm_kernels.cuh"
+#include "../kernels/peer_kernels.cuh"
 
 #include <chrono>
 #include <cstdio>
@@ -98,7 +99,8 @@ struct hmb200_handle {
         size_t buf_bytes = 0, region_bytes = 0;
         uint8_t *region[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; // [rank] own allocation, others IPC-mapped
         bool attached = false;
-        uint64_t products = 0;
+        uint64_t products = 0; // collectives on the replicated buffers so far (fused products + gathers): selects the buffer
+        uint64_t reduces = 0;  // all-reduces so far: selects the slot parity
     } peer;
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
@@ -392,6 +394,16 @@ inline unsigned long long *peer_ctrl_epoch(const hmb200_handle::Peer &pr, int bu
     return reinterpret_cast<unsigned long long *>(pr.region[pr.rank] + 2 * pr.buf_bytes + 128) + buf;
 }
 inline uint32_t *peer_ctrl_done(const hmb200_handle::Peer &pr) { return reinterpret_cast<uint32_t *>(pr.region[pr.rank] + 2 * pr.buf_bytes + 160); }
+// all-reduce area of rank q (after the 256-byte control block): flags[2][8], epoch[2] (local use), then slots[2][8][kPeerReduceMax]
+inline unsigned long long *peer_red_flags(const hmb200_handle::Peer &pr, int q, int parity) {
+    return reinterpret_cast<unsigned long long *>(pr.region[q] + 2 * pr.buf_bytes + 256) + 8 * parity;
+}
+inline unsigned long long *peer_red_epoch(const hmb200_handle::Peer &pr, int parity) {
+    return reinterpret_cast<unsigned long long *>(pr.region[pr.rank] + 2 * pr.buf_bytes + 256 + 128) + parity;
+}
+inline double *peer_red_slots(const hmb200_handle::Peer &pr, int q, int parity) {
+    return reinterpret_cast<double *>(pr.region[q] + 2 * pr.buf_bytes + 512) + (size_t)parity * kMaxPeers * kPeerReduceMax;
+}
 inline int *peer_ctrl_err(const hmb200_handle::Peer &pr) { return reinterpret_cast<int *>(pr.region[pr.rank] + 2 * pr.buf_bytes + 192); }
 
 template <typename T>
@@ -791,6 +803,31 @@ int fused_product(hmb200_handle *h, const double *alpha, const void *in, void **
     return 0;
 }
 
+// all-gather of the local row slabs into the replicated buffer of every rank (the solver's operator input), then the wait
+template <typename T>
+int peer_allgather(hmb200_handle *h, const void *local_slab, void **y_out) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    hmb200_handle::Peer &pr = h->peer;
+    if (!pr.attached) throw std::runtime_error("hmb200_peer_attach has not been called");
+    const int buf = (int)(pr.products & 1);
+    pr.products++;
+    PeerGatherParams p{};
+    p.src = local_slab; p.n_local = h->n_rows; p.n_targets = pr.n_ranks;
+    for (int q = 0; q < pr.n_ranks; q++) {
+        p.dst[q]   = pr.region[q] + (size_t)buf * pr.buf_bytes + (size_t)pr.slab_offset * sizeof(T);
+        p.flags[q] = peer_ctrl_flags(pr, q, buf) + pr.rank;
+    }
+    p.epoch = peer_ctrl_epoch(pr, buf);
+    p.done  = peer_ctrl_done(pr);
+    const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(((int64_t)h->n_rows + 2047) / 2048, 64));
+    peer_gather_kernel<T><<<grid, 256, 0, h->stream>>>(p);
+    peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), 4000000000ll);
+    h->launches += 2;
+    CUDA_CHECK(cudaGetLastError());
+    if (y_out) *y_out = pr.region[pr.rank] + (size_t)buf * pr.buf_bytes;
+    return 0;
+}
+
 template <typename F>
 int guarded(F &&f) {
     try {
@@ -885,7 +922,7 @@ int hmb200_peer_create(hmb200_handle *h, int n_ranks, int rank, int64_t n_global
         if (pr.region[pr.rank]) throw std::runtime_error("peer region already created");
         pr.n_ranks = n_ranks; pr.rank = rank; pr.n_global = n_global; pr.slab_offset = slab_offset;
         pr.buf_bytes    = (((size_t)n_global * h->es) + 255) & ~(size_t)255;
-        pr.region_bytes = 2 * pr.buf_bytes + 256;
+        pr.region_bytes = 2 * pr.buf_bytes + 512 + sizeof(double) * 2 * kMaxPeers * kPeerReduceMax;
         void *r = nullptr;
         CUDA_CHECK(cudaMalloc(&r, pr.region_bytes));
         CUDA_CHECK(cudaMemset(r, 0, pr.region_bytes));
@@ -926,6 +963,38 @@ int hmb200_peer_status(hmb200_handle *h, int *err) {
         if (!h || !err || !h->peer.region[h->peer.rank]) throw std::runtime_error("no peer region");
         CUDA_CHECK(cudaSetDevice(h->device));
         CUDA_CHECK(cudaMemcpy(err, peer_ctrl_err(h->peer), sizeof(int), cudaMemcpyDeviceToHost));
+        return 0;
+    });
+}
+int hmb200_peer_allgather(hmb200_handle *h, const void *local_slab, void **y_replicated) {
+    return guarded([&] {
+        if (!h || !local_slab) throw std::runtime_error("null argument");
+        return h->es == 8 ? peer_allgather<double>(h, local_slab, y_replicated) : peer_allgather<double2>(h, local_slab, y_replicated);
+    });
+}
+int hmb200_peer_allreduce_f64(hmb200_handle *h, double *vals, int n) {
+    return guarded([&] {
+        if (!h || !vals) throw std::runtime_error("null argument");
+        hmb200_handle::Peer &pr = h->peer;
+        if (!pr.attached) throw std::runtime_error("hmb200_peer_attach has not been called");
+        if (n < 0 || n > kPeerReduceMax) throw std::runtime_error("at most 512 doubles per all-reduce");
+        if (n == 0) return 0;
+        CUDA_CHECK(cudaSetDevice(h->device));
+        const int parity = (int)(pr.reduces & 1);
+        pr.reduces++;
+        PeerReduceParams p{};
+        p.vals = vals; p.n = n; p.n_ranks = pr.n_ranks; p.rank = pr.rank;
+        for (int q = 0; q < pr.n_ranks; q++) {
+            p.slots[q] = peer_red_slots(pr, q, parity);
+            p.flags[q] = peer_red_flags(pr, q, parity) + pr.rank;
+        }
+        p.my_flags = peer_red_flags(pr, pr.rank, parity);
+        p.epoch = peer_red_epoch(pr, parity);
+        p.err = peer_ctrl_err(pr);
+        p.max_cycles = 4000000000ll;
+        peer_allreduce_kernel<<<1, 256, 0, h->stream>>>(p);
+        h->launches++;
+        CUDA_CHECK(cudaGetLastError());
         return 0;
     });
 }

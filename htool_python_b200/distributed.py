@@ -192,6 +192,35 @@ class B200DistributedOperator:
         _lib.check(fn(eng._h, one, px, ctypes.byref(out)))
         return self._ybuf[out.value]
 
+    def peer_allgather_(self, local_slab):
+        """replicated vector (view of one of the operator's two peer-mapped buffers) whose slabs are the ranks' `local_slab`
+        tensors: a copy kernel stores the slab into every rank's buffer over NVLink, epoch flags, wait (hmb200_peer_allgather).
+        Collective; the MPI_Allgatherv of add_distributed_operator_vector_product_local_to_local.hpp:44."""
+        import ctypes
+
+        if not self.fused:
+            raise RuntimeError("fused all-gather is not set up on this operator")
+        ptr, _ = self.engine._ptr(local_slab, self.sizes[self.rank], False)
+        out = ctypes.c_void_p()
+        _lib.check(_lib.lib().hmb200_peer_allgather(self.engine._h, ptr, ctypes.byref(out)))
+        return self._ybuf[out.value]
+
+    PEER_ALLREDUCE_MAX = 512  # doubles (include/hmb200.h)
+
+    def peer_allreduce_(self, t):
+        """in-place sum over the ranks of a small float64 / complex128 CUDA tensor, added in rank order on every rank
+        (hmb200_peer_allreduce_f64); collective"""
+        import torch
+
+        if not self.fused:
+            raise RuntimeError("fused all-gather is not set up on this operator")
+        n = t.numel() * (2 if t.is_complex() else 1)
+        if not t.is_contiguous() or t.dtype not in (torch.float64, torch.complex128) or n > self.PEER_ALLREDUCE_MAX:
+            raise ValueError("contiguous float64 / complex128 tensor of at most 512 doubles expected")
+        self.engine.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(_lib.lib().hmb200_peer_allreduce_f64(self.engine._h, t.data_ptr(), n))
+        return t
+
     def peer_status(self) -> int:
         """0, or 1 + the rank whose epoch did not arrive within the wait kernel's bound (synchronises)"""
         import ctypes

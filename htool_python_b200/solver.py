@@ -214,6 +214,8 @@ class CudaKrylovSpace:
         self.es = op.es
         self.world, self.rank, self.group = op.world, op.rank, op.group
         self.off, self.n_local, self.n_global = op.offs[op.rank], op.sizes[op.rank], op.n_target
+        # collectives over the operator's peer-mapped regions (no NCCL call in the iteration) when they are set up
+        self.use_peer = bool(getattr(op, "fused", False))
         self._xg = torch.empty(self.n_global, dtype=self.dtype, device=self.device)   # replicated operator input
         self._xu = torch.empty(self.n_global, dtype=self.dtype, device=self.device)   # user-numbering staging
         self._pin = torch.empty(self.n_global, dtype=self.dtype).pin_memory()
@@ -259,9 +261,13 @@ class CudaKrylovSpace:
         from .distributed import allgather_slabs_
 
         with self.torch.cuda.device(self.device):
-            self._xg[self.off:self.off + self.n_local].copy_(vec)
-            allgather_slabs_(self._xg, self.op.offs, self.op.sizes, 1, self.group)
-            self._permute(False, self._xg, self._xu)
+            if self.use_peer:
+                xg = self.op.peer_allgather_(vec)
+            else:
+                xg = self._xg
+                xg[self.off:self.off + self.n_local].copy_(vec)
+                allgather_slabs_(xg, self.op.offs, self.op.sizes, 1, self.group)
+            self._permute(False, xg, self._xu)
             self._pin.copy_(self._xu, non_blocking=True)
             self.torch.cuda.current_stream(self.device).synchronize()
         return self._pin.numpy().copy()
@@ -272,7 +278,9 @@ class CudaKrylovSpace:
         from .distributed import allgather_slabs_
 
         with self.torch.cuda.device(self.device):
-            if self.world == 1:
+            if self.use_peer:
+                self.op.engine.add_vector_product("N", 1.0, self.op.peer_allgather_(vin), 0.0, vout)
+            elif self.world == 1:
                 self.op.engine.add_vector_product("N", 1.0, vin, 0.0, vout)
             else:
                 self._xg[self.off:self.off + self.n_local].copy_(vin)
@@ -281,6 +289,8 @@ class CudaKrylovSpace:
 
     # ---- reductions ---------------------------------------------------------------------------------------------
     def _allreduce(self, t):
+        if self.use_peer and t.numel() * (2 if t.is_complex() else 1) <= self.op.PEER_ALLREDUCE_MAX:
+            return self.op.peer_allreduce_(t)
         if self.world > 1:
             import torch.distributed as dist
 

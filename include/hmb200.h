@@ -144,6 +144,13 @@ int hmb200_peer_create(hmb200_handle *h, int n_ranks, int rank, int64_t n_global
 int hmb200_peer_attach(hmb200_handle *h, const unsigned char *ipc_handles);
 int hmb200_peer_buffer(hmb200_handle *h, int index, void **ptr);
 int hmb200_peer_status(hmb200_handle *h, int *err);
+/* the solver's two collectives on the same peer regions (no NCCL / MPI on the iteration path):
+ *   hmb200_peer_allgather     local slab (n_rows elements, device) -> replicated vector on every rank
+ *                             (MPI_Allgatherv of ..._vector_product_local_to_local.hpp:44); counts as one collective of step 3
+ *   hmb200_peer_allreduce_f64 in-place sum over the ranks of n <= 512 device doubles, added in rank order on every rank
+ *                             (the MPI_Allreduce of HPDDM's Arnoldi step, lib/hpddm/include/HPDDM_iterative.hpp:549,740) */
+int hmb200_peer_allgather(hmb200_handle *h, const void *local_slab, void **y_replicated);
+int hmb200_peer_allreduce_f64(hmb200_handle *h, double *vals, int n);
 int hmb200_vector_product_allgather_d(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated);
 int hmb200_vector_product_allgather_z(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated);
 

@@ -96,3 +96,30 @@ def test_device_gmres_block_of_rhs_and_errors():
     with pytest.raises(RuntimeError, match="Wrong size"):
         solver.solve(np.zeros(flat.n_rows + 1), np.zeros(flat.n_rows + 1))
     op.close()
+
+
+@pytest.mark.parametrize("case", [0, 3, 4])
+def test_device_gmres_over_peer_collectives_single_rank(case):
+    """the solver on the peer-memory collectives (hmb200_peer_allgather / hmb200_peer_allreduce_f64: copy kernel + epoch flags,
+    one-CTA all-reduce) with one rank: same HPDDM counts; the 2-rank version runs in test_gpu_parity.py::test_distributed_operator"""
+    from htool_python_b200 import B200DistributedOperator, B200Solver
+
+    g = gmres_golden()[case]
+    flat, _ = helpers.load_golden(g["fixture"])
+    op = B200DistributedOperator(flat, [(0, flat.n_rows)], fused_allgather=True)
+    solver = B200Solver(op)
+    assert op.fused and solver.space.use_peer
+    x = np.zeros(flat.n_rows, flat.np_dtype)
+    it = solver.solve(x, g["b"], g["args"])
+    assert it == g["iterations"] and solver.last_info["operator_calls"] == g["calls"]
+    check_solution(flat, g, x, case, x_tol=[10 * t for t in X_TOL])
+    assert op.peer_status() == 0
+    # the all-reduce alone: in-place, rank-ordered sum (one rank: identity), real and complex
+    import torch
+
+    for t in (torch.arange(7, dtype=torch.float64, device="cuda"), torch.arange(5, dtype=torch.float64, device="cuda") * (1 + 2j)):
+        ref = t.clone()
+        for _ in range(3):
+            op.peer_allreduce_(t)
+        assert torch.equal(torch.view_as_real(t) if t.is_complex() else t, torch.view_as_real(ref) if ref.is_complex() else ref)
+    op.close()
