@@ -23,11 +23,38 @@ solver = B200Solver(op)
 b = op.matvec(np.random.default_rng(3).random(n))
 x = np.zeros(n)
 opts = f"-hpddm_krylov_method gmres -hpddm_schwarz_method none -hpddm_tol 1e-12 -hpddm_gmres_restart 40 -hpddm_max_it {max_it}"
-solver.solve(x, b, opts)
-x[:] = 0
-torch.cuda.synchronize()
-t0 = time.perf_counter()
-it = solver.solve(x, b, opts)
-torch.cuda.synchronize()
-dt = time.perf_counter() - t0
-print(f"gmres-profile: n={n} iterations={it} solve {dt * 1e3:.2f} ms = {dt * 1e3 / it:.3f} ms/iteration, kernel launches (krylov/permute) {solver.space.kernel_launches}")
+import ctypes  # noqa: E402
+
+from htool_python_b200 import _lib  # noqa: E402
+
+
+def run(label, extra=""):
+    x[:] = 0
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    it = solver.solve(x, b, opts + extra)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    print(f"gmres-profile: {label:34s} n={n} iterations={it} solve {dt * 1e3:8.2f} ms = {dt * 1e3 / it:.3f} ms/iteration", flush=True)
+
+
+for k in range(3):
+    run(f"solve #{k + 1} (graphs on, speculation on)")
+if os.environ.get("GMRES_PROFILE_VARIANTS"):
+    solver.opt["speculate"] = False
+    run("speculation off")
+    solver.opt["speculate"] = True
+    _lib.check(_lib.lib().hmb200_set_graphs(hb.engine._h, 0))
+    run("graphs off")
+    run("graphs off (2nd)")
+    # the product alone, back to back, for reference
+    xc = torch.rand(n, dtype=torch.float64, device="cuda")
+    yc = torch.zeros(n, dtype=torch.float64, device="cuda")
+    for _ in range(3):
+        hb.engine.add_vector_product("N", 1.0, xc, 0.0, yc)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(50):
+        hb.engine.add_vector_product("N", 1.0, xc, 0.0, yc)
+    torch.cuda.synchronize()
+    print(f"gmres-profile: product alone {(time.perf_counter() - t0) * 20:.3f} ms", flush=True)
