@@ -805,21 +805,23 @@ int fused_product(hmb200_handle *h, const double *alpha, const void *in, void **
 
 // all-gather of the local row slabs into the replicated buffer of every rank (the solver's operator input), then the wait
 template <typename T>
-int peer_allgather(hmb200_handle *h, const void *local_slab, void **y_out) {
+int peer_allgather(hmb200_handle *h, const void *local_slab, void **y_out, int64_t elem_offset = -1, int64_t count = -1) {
     CUDA_CHECK(cudaSetDevice(h->device));
     hmb200_handle::Peer &pr = h->peer;
     if (!pr.attached) throw std::runtime_error("hmb200_peer_attach has not been called");
+    if (elem_offset < 0) { elem_offset = pr.slab_offset; count = h->n_rows; } // default: this rank's row slab
+    if (count < 0 || elem_offset + count > pr.n_global) throw std::runtime_error("range does not fit the replicated vector");
     const int buf = (int)(pr.products & 1);
     pr.products++;
     PeerGatherParams p{};
-    p.src = local_slab; p.n_local = h->n_rows; p.n_targets = pr.n_ranks;
+    p.src = local_slab; p.n_local = count; p.n_targets = pr.n_ranks;
     for (int q = 0; q < pr.n_ranks; q++) {
-        p.dst[q]   = pr.region[q] + (size_t)buf * pr.buf_bytes + (size_t)pr.slab_offset * sizeof(T);
+        p.dst[q]   = pr.region[q] + (size_t)buf * pr.buf_bytes + (size_t)elem_offset * sizeof(T);
         p.flags[q] = peer_ctrl_flags(pr, q, buf) + pr.rank;
     }
     p.epoch = peer_ctrl_epoch(pr, buf);
     p.done  = peer_ctrl_done(pr);
-    const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(((int64_t)h->n_rows + 2047) / 2048, 64));
+    const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>((count + 2047) / 2048, 64));
     peer_gather_kernel<T><<<grid, 256, 0, h->stream>>>(p);
     peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), 4000000000ll);
     h->launches += 2;
@@ -970,6 +972,12 @@ int hmb200_peer_allgather(hmb200_handle *h, const void *local_slab, void **y_rep
     return guarded([&] {
         if (!h || !local_slab) throw std::runtime_error("null argument");
         return h->es == 8 ? peer_allgather<double>(h, local_slab, y_replicated) : peer_allgather<double2>(h, local_slab, y_replicated);
+    });
+}
+int hmb200_peer_allgather_range(hmb200_handle *h, const void *local_part, int64_t elem_offset, int64_t count, void **y_replicated) {
+    return guarded([&] {
+        if (!h || (!local_part && count > 0) || elem_offset < 0) throw std::runtime_error("null argument / negative offset");
+        return h->es == 8 ? peer_allgather<double>(h, local_part, y_replicated, elem_offset, count) : peer_allgather<double2>(h, local_part, y_replicated, elem_offset, count);
     });
 }
 int hmb200_peer_allreduce_f64(hmb200_handle *h, double *vals, int n) {

@@ -118,6 +118,7 @@ class B200DistributedOperator:
         self._x = {}  # mu -> (x_cluster, y_cluster) replicated device buffers
         self._pin = {}
         self.fused = False
+        self.split_input_upload = True  # `matvec` on several GPUs: each rank uploads 1/P of x, NVLink exchange (needs identical x on all ranks)
         self._ybuf = None
         if fused_allgather is None:
             fused_allgather = self.world > 1
@@ -205,6 +206,14 @@ class B200DistributedOperator:
         _lib.check(_lib.lib().hmb200_peer_allgather(self.engine._h, ptr, ctypes.byref(out)))
         return self._ybuf[out.value]
 
+    def _peer_allgather_range(self, part, offset, count):
+        import ctypes
+
+        out = ctypes.c_void_p()
+        self.engine.set_stream(__import__("torch").cuda.current_stream(self.device).cuda_stream)
+        _lib.check(_lib.lib().hmb200_peer_allgather_range(self.engine._h, part.data_ptr(), int(offset), int(count), ctypes.byref(out)))
+        return self._ybuf[out.value]
+
     PEER_ALLREDUCE_MAX = 512  # doubles (include/hmb200.h)
 
     def peer_allreduce_(self, t):
@@ -228,6 +237,23 @@ class B200DistributedOperator:
         err = ctypes.c_int(0)
         _lib.check(_lib.lib().hmb200_peer_status(self.engine._h, ctypes.byref(err)))
         return err.value
+
+    def matvec_cluster_transposed_(self, x_cluster, y_cluster, trans: str = "T"):
+        """y_cluster (replicated, length n_source) = op(A) x_cluster with op = transpose ('T') or conjugate transpose ('C'):
+        every rank applies op(A_p) to ITS slab of x and the full-length results are summed over the ranks -- the `trans != 'N'`
+        branch of add_distributed_operator_vector_product_global_to_global.hpp:63-84 (MPI_Allreduce :78).  The engine must have
+        been created with build_transpose=1."""
+        import torch.distributed as dist
+
+        if trans not in ("T", "C"):
+            raise ValueError("trans must be 'T' or 'C'")
+        o, s = self.offs[self.rank], self.sizes[self.rank]
+        self.engine.add_vector_product(trans, 1.0, x_cluster[o:o + s], 0.0, y_cluster)
+        if self.world > 1:
+            import torch
+
+            dist.all_reduce(torch.view_as_real(y_cluster) if y_cluster.is_complex() else y_cluster, group=self.group)
+        return y_cluster
 
     def matmat_cluster_(self, X_cluster, Y_cluster, mu: int):
         """row-major (n x mu) blocks (add_distributed_operator_matrix_product_row_major_global_to_global.hpp:18-84)."""
@@ -283,10 +309,20 @@ class B200DistributedOperator:
         (xu, xc, yc, yu), (pin_x, pin_y) = self._buffers(1)
         with torch.cuda.device(self.device):
             src = self._as_pinned_tensor(x)
-            if src is None:
-                pin_x.numpy()[:] = x.astype(self.np_dtype, copy=False)
-                src = pin_x
-            xu.copy_(src, non_blocking=True)
+            if self.fused and self.world > 1 and self.split_input_upload and self.n_source == self.n_target:
+                # the input is replicated on the hosts (the contract of the global-to-global product): every rank uploads
+                # only ITS 1/P chunk of the user-numbered vector and the chunks are exchanged over NVLink
+                c0, c1 = self.rank * self.n_source // self.world, (self.rank + 1) * self.n_source // self.world
+                if src is None:
+                    pin_x.numpy()[c0:c1] = x[c0:c1].astype(self.np_dtype, copy=False)
+                    src = pin_x
+                xu[c0:c1].copy_(src[c0:c1], non_blocking=True)
+                xu = self._peer_allgather_range(xu[c0:c1], c0, c1 - c0)
+            else:
+                if src is None:
+                    pin_x.numpy()[:] = x.astype(self.np_dtype, copy=False)
+                    src = pin_x
+                xu.copy_(src, non_blocking=True)
             self._permute(True, self.perm_s, self.n_source, xu, xc, 1)     # global_to_root_cluster (:108)
             yc = self.matvec_cluster_fused_(xc) if self.fused else self.matvec_cluster_(xc, yc)
             self._permute(False, self.perm_t, self.n_target, yc, yu, 1)    # root_cluster_to_global (:117)

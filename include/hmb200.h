@@ -150,6 +150,9 @@ int hmb200_peer_status(hmb200_handle *h, int *err);
  *   hmb200_peer_allreduce_f64 in-place sum over the ranks of n <= 512 device doubles, added in rank order on every rank
  *                             (the MPI_Allreduce of HPDDM's Arnoldi step, lib/hpddm/include/HPDDM_iterative.hpp:549,740) */
 int hmb200_peer_allgather(hmb200_handle *h, const void *local_slab, void **y_replicated);
+/* the same with an arbitrary disjoint range [elem_offset, elem_offset+count) per rank (e.g. equal chunks of a user-numbered
+ * input that every rank holds on the host: each rank uploads 1/P of it and the chunks are exchanged over NVLink) */
+int hmb200_peer_allgather_range(hmb200_handle *h, const void *local_part, int64_t elem_offset, int64_t count, void **y_replicated);
 int hmb200_peer_allreduce_f64(hmb200_handle *h, double *vals, int n);
 int hmb200_vector_product_allgather_d(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated);
 int hmb200_vector_product_allgather_z(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated);

@@ -262,6 +262,22 @@ def _dist_worker(rank, world, port, q, kernel="laplace_reg"):
         op_nccl = B200DistributedOperator(slab, tree.partition, fused_allgather=False)
         same = same and np.array_equal(op_nccl * x, y) and not op_nccl.fused
         status = op.peer_status() if op.fused else 0
+        # transposed / conjugate-transposed distributed product: sum over the ranks of op(A_p) x_p (all-reduce driver)
+        import torch
+
+        et = 0.0
+        op_t = B200DistributedOperator(slab, tree.partition, fused_allgather=False, build_transpose=1)
+        xt = helpers.rand_vec(rng, n, dt)
+        for tr in ["T"] + (["C"] if dt == np.complex128 else []):
+            yt = torch.zeros(n, dtype=op_t.torch_dtype, device=op_t.device)
+            op_t.matvec_cluster_transposed_(torch.from_numpy(xt).to(op_t.device), yt, tr)
+            yt_ref = np.zeros(n, dt)
+            for p, f in enumerate(flats):
+                part = np.zeros(n, dt)
+                fo.add_vector_product(f, tr, 1.0, np.ascontiguousarray(xt[offs[p]:offs[p] + sizes[p]]), 0.0, part)
+                yt_ref += part
+            et = max(et, rel_err(yt.cpu().numpy(), yt_ref))
+        op_t.close()
         # device GMRES on the distributed operator vs the oracle GMRES over the restated slabs
         from htool_python_b200 import B200Solver
         from oracle import gmres_oracle as go
@@ -280,7 +296,7 @@ def _dist_worker(rank, world, port, q, kernel="laplace_reg"):
         xs = np.zeros(n, dt)
         it = B200Solver(op).solve(xs, b, args)
         x_ref, it_ref, _ = go.gmres(matvec, b, **go.parse_hpddm_args(args))
-        q.put((rank, rel_err(y, y_ref), rel_err(Y, Y_ref), bool(Y.flags.f_contiguous), bool(op.fused), same, status, it, it_ref, rel_err(xs, x_ref)))
+        q.put((rank, rel_err(y, y_ref), rel_err(Y, Y_ref), bool(Y.flags.f_contiguous), bool(op.fused), same, status, it, it_ref, rel_err(xs, x_ref), et))
         op_nccl.close()
         op.close()
     finally:
@@ -311,8 +327,8 @@ def test_distributed_operator(world, kernel):
     res = [q.get(timeout=300) for _ in range(world)]
     for p in procs:
         p.join(timeout=120)
-    for rank, e1, e2, f_order, fused, same, status, it, it_ref, ex in res:
-        assert e1 < TOL and e2 < TOL and f_order, (rank, e1, e2)
+    for rank, e1, e2, f_order, fused, same, status, it, it_ref, ex, et in res:
+        assert e1 < TOL and e2 < TOL and et < TOL and f_order, (rank, e1, e2, et)
         assert same and status == 0, (rank, same, status)
         assert fused == (world > 1), "the fused all-gather must be the path that runs on several GPUs"
         assert it == it_ref and 0 < it < 100 and ex < 1e-7, (rank, it, it_ref, ex)
