@@ -348,7 +348,10 @@ def run_b200(args):
                        "stored_coefficients_rank0": flat.stored_coefficients, "leaves_rank0": flat.n_leaves,
                        "assembly": "reference HMatrixTreeBuilder (OpenMP, native generator), outside the timed region", **build_t},
             "clocks": clocks,
-            "e2e": {"value": round(mu / e2e_step, 3), "unit": UNIT, "h2d_bytes_per_step": es * n * mu, "d2h_bytes_per_step": es * n * mu,
+            # bytes summed over the ranks: at N > 1 the single-RHS `matvec` uploads 1/N of x per rank (chunks exchanged over
+            # NVLink); every rank downloads the full y (the reference API returns the replicated result on every rank)
+            "e2e": {"value": round(mu / e2e_step, 3), "unit": UNIT,
+                    "h2d_bytes_per_step": es * n * mu * (1 if (world == 1 or (mu == 1 and op.fused)) else world), "d2h_bytes_per_step": es * n * mu * world,
                     "ms_per_step": round(e2e_step * 1e3, 4)},
             "gpu_launches": int(launches),
             "roofline": roofline,
