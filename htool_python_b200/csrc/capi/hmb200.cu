@@ -385,7 +385,6 @@ PackedOp &select_op(hmb200_handle *h, char trans) {
     return h->ops[idx];
 }
 
-// runs out = beta*out + alpha*op(A)*xz[0:n_in] on the handle's stream; x must already be in xz; y is a device pointer
 // control block of rank q's shared region (after the two replicated buffers)
 inline unsigned long long *peer_ctrl_flags(const hmb200_handle::Peer &pr, int q, int buf) {
     return reinterpret_cast<unsigned long long *>(pr.region[q] + 2 * pr.buf_bytes) + 8 * buf;
@@ -406,6 +405,8 @@ inline double *peer_red_slots(const hmb200_handle::Peer &pr, int q, int parity) 
 }
 inline int *peer_ctrl_err(const hmb200_handle::Peer &pr) { return reinterpret_cast<int *>(pr.region[pr.rank] + 2 * pr.buf_bytes + 192); }
 
+// runs out = beta*out + alpha*op(A)*xz[0:n_in] on the handle's stream; x must already be in xz; y is a device pointer;
+// peer_buf >= 0: the phase-2 epilogue also stores the rows into buffer `peer_buf` of every rank and publishes the epoch
 template <typename T>
 void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, void *y, const int32_t *out_perm, int peer_buf = -1) {
     const Options &o = h->opt;
