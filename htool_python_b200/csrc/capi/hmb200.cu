@@ -8,6 +8,7 @@
 
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <stdexcept>
@@ -101,6 +102,7 @@ struct hmb200_handle {
         bool attached = false;
         uint64_t products = 0; // collectives on the replicated buffers so far (fused products + gathers): selects the buffer
         uint64_t reduces = 0;  // all-reduces so far: selects the slot parity
+        long long wait_cycles = 240000000000ll; // bound of the device-side waits (~2 minutes; HMB200_PEER_TIMEOUT_S overrides)
     } peer;
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
@@ -796,7 +798,7 @@ int fused_product(hmb200_handle *h, const double *alpha, const void *in, void **
     run_cached(h, key, [&] {
         CUDA_CHECK(cudaMemcpyAsync(h->xz, in, in_b, cudaMemcpyDeviceToDevice, h->stream));
         run_product<T>(h, po, alpha, zero, ybuf + (size_t)pr.slab_offset * sizeof(T), nullptr, buf);
-        peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), 4000000000ll);
+        peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), pr.wait_cycles);
         h->launches++;
         CUDA_CHECK(cudaGetLastError());
     });
@@ -824,7 +826,7 @@ int peer_allgather(hmb200_handle *h, const void *local_slab, void **y_out, int64
     p.done  = peer_ctrl_done(pr);
     const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>((count + 2047) / 2048, 64));
     peer_gather_kernel<T><<<grid, 256, 0, h->stream>>>(p);
-    peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), 4000000000ll);
+    peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), pr.wait_cycles);
     h->launches += 2;
     CUDA_CHECK(cudaGetLastError());
     if (y_out) *y_out = pr.region[pr.rank] + (size_t)buf * pr.buf_bytes;
@@ -924,6 +926,14 @@ int hmb200_peer_create(hmb200_handle *h, int n_ranks, int rank, int64_t n_global
         hmb200_handle::Peer &pr = h->peer;
         if (pr.region[pr.rank]) throw std::runtime_error("peer region already created");
         pr.n_ranks = n_ranks; pr.rank = rank; pr.n_global = n_global; pr.slab_offset = slab_offset;
+        {   // a peer that never arrives must not hang the GPU for ever: the waits give up after this many SM clocks and set the
+            // error word (hmb200_peer_status); ranks may legitimately be seconds apart (host-side work), hence the generous default
+            int khz = 0;
+            cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, h->device);
+            const char *ev = std::getenv("HMB200_PEER_TIMEOUT_S");
+            const double secs = ev && std::atof(ev) > 0 ? std::atof(ev) : 120.0;
+            pr.wait_cycles = (long long)(secs * 1e3 * (khz > 0 ? khz : 1965000));
+        }
         pr.buf_bytes    = (((size_t)n_global * h->es) + 255) & ~(size_t)255;
         pr.region_bytes = 2 * pr.buf_bytes + 512 + sizeof(double) * 2 * kMaxPeers * kPeerReduceMax;
         void *r = nullptr;
@@ -1000,7 +1010,7 @@ int hmb200_peer_allreduce_f64(hmb200_handle *h, double *vals, int n) {
         p.my_flags = peer_red_flags(pr, pr.rank, parity);
         p.epoch = peer_red_epoch(pr, parity);
         p.err = peer_ctrl_err(pr);
-        p.max_cycles = 4000000000ll;
+        p.max_cycles = pr.wait_cycles;
         peer_allreduce_kernel<<<1, 256, 0, h->stream>>>(p);
         h->launches++;
         CUDA_CHECK(cudaGetLastError());

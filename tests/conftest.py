@@ -9,6 +9,10 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
         sys.path.insert(0, p)
 
 
+# a peer that never arrives makes the device-side waits of the fused all-gather give up after this many seconds (default 120)
+os.environ.setdefault("HMB200_PEER_TIMEOUT_S", "20")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 
