@@ -58,3 +58,28 @@ if os.environ.get("GMRES_PROFILE_VARIANTS"):
         hb.engine.add_vector_product("N", 1.0, xc, 0.0, yc)
     torch.cuda.synchronize()
     print(f"gmres-profile: product alone {(time.perf_counter() - t0) * 20:.3f} ms", flush=True)
+if os.environ.get("GMRES_PROFILE_VARIANTS"):
+    # the device pipeline of one iteration without any host read: product + dots + combine (+norm) + scale on a 20-vector basis
+    sp = solver.space
+    V = sp.basis(41)
+    V.data.normal_()
+    _lib.check(_lib.lib().hmb200_set_graphs(hb.engine._h, 1))
+
+    def pipeline(n_it, with_krylov=True):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        ev0.record()
+        for it_ in range(n_it):
+            i = it_ % 39
+            w = V.row(i + 1)
+            sp.matvec(V.row(i), w)
+            if with_krylov:
+                h = sp.dots(V, 0, 20, w)
+                n2 = sp.combine(V, 0, 20, h, -1.0, w, want_norm=True)
+                sp.scale(w, n2)
+        ev1.record()
+        torch.cuda.synchronize()
+        return ev0.elapsed_time(ev1) / n_it
+
+    pipeline(80)
+    print(f"gmres-profile: device pipeline without host reads: product only {pipeline(120, False):.3f} ms, product + dots/combine/scale (k=20) {pipeline(120):.3f} ms per iteration", flush=True)
