@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--rhs", type=int, default=1, help="right-hand sides per step (64 = BASELINE.json configs[3], DMMA multi-RHS path; off-metric)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gmres", action="store_true", help="also solve A x = b with the device-resident GMRES (BASELINE.json configs[4]; adds a 'gmres' object)")
+    ap.add_argument("--gmres-block", type=int, default=0, help="with --gmres: also solve a block of this many right-hand sides in lockstep "
+                    "(HPDDM's GMRES with mu > 1 on the multi-RHS product) and column by column, tol 1e-3")
     ap.add_argument("--gmres-args", default="-hpddm_krylov_method gmres -hpddm_schwarz_method none -hpddm_variant right -hpddm_tol 1e-6 -hpddm_gmres_restart 40 -hpddm_max_it 200")
     ap.add_argument("--engine-opts", default="", help="k=v,k=v overrides of hmb200_options (tuning runs)")
     return ap.parse_args()
@@ -418,6 +420,28 @@ def run_gmres(args, op, flat, tree, H, world, rank, dev, threads, log, barrier):
         _, it3_cpu, _ = helpers_ref.hpddm_solve(lambda v: fn(H.address, np.ascontiguousarray(v), True), b, args=loose)
         out["tol_1e-3"].update({"reference_iterations": int(it3_cpu), "reference_solve_s": round(time.perf_counter() - t0, 3)})
     log(f"gmres tol 1e-3: {out['tol_1e-3']}")
+    if args.gmres_block > 1:
+        mu = args.gmres_block
+        B = np.asfortranarray(dop @ np.asfortranarray(np.random.default_rng(4).random((n, mu))))
+        X = np.zeros_like(B, order="F")
+        solver.solve(X, B, loose + " -hpddm_max_it 3")  # warm-up (block buffers)
+        blk = {"mu": mu, "args": loose}
+        for mode in ("lockstep", "columns"):
+            X[:] = 0
+            barrier()
+            t0 = time.perf_counter()
+            itb = solver.solve(X, B, loose + " -hpddm_block_rhs " + mode)
+            torch.cuda.synchronize()
+            dtb = time.perf_counter() - t0
+            R = (dop @ X) - B
+            blk[mode] = {"iterations": int(itb), "operator_calls": int(solver.get_information()["nb_mat_vec_prod"]), "solve_s": round(dtb, 4),
+                         "max_true_residual": float(max(np.linalg.norm(R[:, c]) / np.linalg.norm(B[:, c]) for c in range(mu)))}
+            if mode == "lockstep":
+                X_lock = X.copy()
+        blk["max_rel_diff_lockstep_vs_columns"] = float(max(np.linalg.norm(X_lock[:, c] - X[:, c]) / np.linalg.norm(X[:, c]) for c in range(mu)))
+        solver.set_hpddm_args("-hpddm_block_rhs lockstep")
+        out["block"] = blk
+        log(f"gmres block: {blk}")
     return out
 
 

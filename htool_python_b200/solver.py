@@ -14,8 +14,8 @@ Here every rank keeps its slab of b, x and of the Krylov basis in HBM; one itera
   with two tiny all-reduces, and ONE small device->host read (the new Hessenberg column) for the Givens update and the
   convergence test, which stay on the host exactly as HPDDM does them (HPDDM_iterative.hpp:748-765, :88-91).
 The control flow (restart, `hasConverged` sentinel, max_it handling, returned iteration count) follows HPDDM_GMRES.hpp
-line by line so that iteration counts match the reference's.  Scope: one right-hand side per solve call (a block of
-right-hand sides is solved column by column), no preconditioner (`-hpddm_schwarz_method none`); Schwarz / GenEO
+line by line so that iteration counts match the reference's.  Scope: one right-hand side, or a block of mu right-hand sides
+advanced in lockstep on the multi-right-hand-side product (`gmres_block_driver`), no preconditioner (`-hpddm_schwarz_method none`); Schwarz / GenEO
 preconditioners are outside the hot path (out of scope).
 """
 from __future__ import annotations
@@ -187,12 +187,121 @@ def gmres_driver(sp, b_host, x_host, opt: dict):
     return x_out, it, dict(operator_calls=calls, residuals=residuals, converged=bool(j <= max_it), norm_b=norm_b, speculative_unused=unused)
 
 
+def gmres_block_driver(sp, B_host, X_host, opt: dict):
+    """GMRES on a block of mu right-hand sides, control flow of IterativeMethod::GMRES with mu > 1
+    (HPDDM_GMRES.hpp:30-196): mu independent recurrences advanced in LOCKSTEP -- ONE operator call on the n x mu block per
+    iteration (the multi-right-hand-side DMMA kernel, as HPDDMOperator::GMV with mu > 1 calls the row-major matrix product,
+    wrapper_hpddm.hpp:102-145), one Hessenberg / rotation set / `hasConverged` entry per column (HPDDM_iterative.hpp:88-91,
+    :722-768); the loop ends when no column is left at the sentinel, and the solution update uses each column's own dimension
+    (computeMin / addSol, :283-326).  Per iteration the host reads the mu new Hessenberg columns in one transfer; the
+    reductions of all columns share one all-reduce (orthogonalization :549 reduces the k x mu block at once).
+    B_host, X_host: (n, mu).  Returns (X_host_new, iterations, info)."""
+    tol, max_it = float(opt["tol"]), int(opt["max_it"])
+    m = min(int(opt["gmres_restart"]), max_it)
+    mgs = str(opt.get("orthogonalization", "cgs")).lower() in ("mgs", "1")
+    eps = np.finfo(np.float64).eps
+    if abs(tol) < eps:
+        tol = 4 * eps
+    mu = int(B_host.shape[1])
+    cols = range(mu)
+    real0 = lambda a: float(np.asarray(a).real.reshape(-1)[0])  # noqa: E731
+    b, x = sp.block(mu), sp.block(mu)
+    sp.set_block_from_user(b, B_host)
+    sp.set_block_from_user(x, X_host)
+    norm_b = [math.sqrt(real0(v)) for v in sp.host(sp.allreduce_many([sp.norm2(b[c], reduce=False) for c in cols]))]
+    norm_b = [1.0 if v < HPDDM_EPS else v for v in norm_b]
+    VB = sp.block_basis(m + 1, mu)
+    hess = [_Hessenberg(m, sp.np_dtype) for _ in cols]
+    conv = [-m] * mu
+    calls, residuals = 0, []
+
+    def update(dims):
+        for c in cols:
+            if dims[c]:
+                sp.combine(VB.col(c), 0, dims[c], sp.upload(hess[c].solve(dims[c])), 1.0, x[c], want_norm=False)
+
+    j = 1
+    while j <= max_it:
+        V0 = VB.block(0)
+        sp.matmat(x, V0)
+        calls += 1
+        beta2_dev = sp.allreduce_many([sp.axpby_norm(1.0, b[c], -1.0, V0[c], V0[c], reduce=False) for c in cols])  # V_0 = B - A X
+        beta2 = [real0(v) for v in sp.host(beta2_dev)]
+        if j == 1 and any(v < eps ** 2 for v in beta2):  # HPDDM_GMRES.hpp:87-90, any column
+            j, conv = 0, [0] * mu
+            break
+        for c in cols:
+            if conv[c] > 0:
+                conv[c] = 0
+            hess[c].start(math.sqrt(beta2[c]))
+            sp.scale(V0[c], beta2_dev[c])
+        i = 0
+        while i < m and j <= max_it:
+            W = VB.block(i + 1)
+            sp.matmat(VB.block(i), W)
+            calls += 1
+            if mgs:  # HPDDM_iterative.hpp:522-540: one reduction of mu values per basis vector
+                hk_all = []
+                for k in range(i + 1):
+                    hk = sp.allreduce_many([sp.dots(VB.col(c), k, 1, W[c], reduce=False) for c in cols])
+                    n2_raw = [sp.combine(VB.col(c), k, 1, hk[c], -1.0, W[c], want_norm=(k == i), reduce=False) for c in cols]
+                    hk_all.append(hk)
+                n2_dev = sp.allreduce_many(n2_raw)
+                got = sp.host([hk_all[k][c] for c in cols for k in range(i + 1)] + n2_dev)
+                hcols = [np.array([got[c * (i + 1) + k][0] for k in range(i + 1)]) for c in cols]
+            else:  # classical Gram-Schmidt (:541-552)
+                h_dev = sp.allreduce_many([sp.dots(VB.col(c), 0, i + 1, W[c], reduce=False) for c in cols])
+                n2_dev = sp.allreduce_many([sp.combine(VB.col(c), 0, i + 1, h_dev[c], -1.0, W[c], want_norm=True, reduce=False) for c in cols])
+                got = sp.host(h_dev + n2_dev)
+                hcols = got[:mu]
+            if i < m - 1:
+                for c in cols:
+                    sp.scale(W[c], n2_dev[c])
+            res = [hess[c].push(i, hcols[c], real0(got[len(got) - mu + c])) for c in cols]
+            i += 1
+            residuals.append([res[c] / norm_b[c] for c in cols])
+            for c in cols:
+                if conv[c] == -m and ((tol > 0 and res[c] / norm_b[c] <= tol) or (tol < 0 and res[c] <= -tol)):
+                    conv[c] = i
+            if -m not in conv:
+                i = 0
+                break
+            j += 1
+        if j != max_it + 1 and i == m:  # restart
+            update([abs(c) for c in conv])
+        else:
+            break
+    if j == max_it + 1 and m > 0:
+        rem = max_it % m
+        conv = [(rem if rem > 0 else -c) if c < 0 else c for c in conv]
+    if j != 0:
+        update([abs(c) for c in conv])
+    it = min(j, max_it)
+    return sp.get_block_to_user(x), it, dict(operator_calls=calls, residuals=residuals, converged=bool(j <= max_it), norm_b=norm_b,
+                                            converged_at=list(conv), speculative_unused=0, block=mu)
+
+
 class _Basis:
     def __init__(self, data, n):
         self.data, self.n = data, n  # (count, n) row-contiguous device tensor
 
     def row(self, i):
         return self.data[i]
+
+
+class _BlockBasis:
+    """(count, mu, n) storage of a block Krylov basis: HPDDM's layout v[i] + nu * n (HPDDM_GMRES.hpp:47-53), so the basis of
+    ONE column is a set of vectors with leading dimension mu * n (ldv of the gemv calls, HPDDM_iterative.hpp:542)"""
+
+    def __init__(self, data):
+        self.data = data
+        self.mu, self.n = int(data.shape[1]), int(data.shape[2])
+
+    def block(self, i):
+        return self.data[i]
+
+    def col(self, c):
+        return _Basis(self.data[:, c], self.mu * self.n)
 
 
 class CudaKrylovSpace:
@@ -222,6 +331,7 @@ class CudaKrylovSpace:
         self._scratch = None
         self._hpin, self._hev = None, None
         self._k_max = 0
+        self._blk = {}
         self.kernel_launches = 0
 
     # ---- storage ------------------------------------------------------------------------------------------------
@@ -231,6 +341,26 @@ class CudaKrylovSpace:
     def basis(self, count):
         self._reserve(count)
         return _Basis(self.torch.zeros((count, self.n_local), dtype=self.dtype, device=self.device), self.n_local)
+
+    def block(self, mu):
+        return self.torch.zeros((mu, self.n_local), dtype=self.dtype, device=self.device)
+
+    def block_basis(self, count, mu):
+        self._reserve(count)
+        return _BlockBasis(self.torch.zeros((count, mu, self.n_local), dtype=self.dtype, device=self.device))
+
+    def set_block_from_user(self, blk, host):
+        host = np.asarray(host)
+        if host.ndim != 2 or host.shape != (self.n_global, blk.shape[0]):
+            raise RuntimeError("Wrong size for right-hand side or solution")
+        for c in range(blk.shape[0]):
+            self.set_from_user(blk[c], host[:, c])
+
+    def get_block_to_user(self, blk):
+        out = np.empty((self.n_global, blk.shape[0]), dtype=self.np_dtype, order="F")
+        for c in range(blk.shape[0]):
+            out[:, c] = self.get_to_user(blk[c])
+        return out
 
     def _reserve(self, k):
         if self._scratch is None or k > self._k_max:
@@ -287,7 +417,36 @@ class CudaKrylovSpace:
                 allgather_slabs_(self._xg, self.op.offs, self.op.sizes, 1, self.group)
                 self.op.engine.add_vector_product("N", 1.0, self._xg, 0.0, vout)
 
+    def matmat(self, vin, vout):
+        """vout = A_p * allgather(vin) for (mu, n_local) column blocks: HPDDMOperator::GMV with mu > 1 transposes to row-major,
+        calls the row-major local-to-local matrix product and transposes back (wrapper_hpddm.hpp:108-116, :129-135;
+        add_distributed_operator_matrix_product_row_major_local_to_local.hpp:25-95).  The product is the multi-RHS DMMA kernel."""
+        from .distributed import allgather_slabs_
+
+        mu = int(vin.shape[0])
+        if mu not in self._blk:
+            self._blk[mu] = (self.torch.empty(self.n_global * mu, dtype=self.dtype, device=self.device),
+                             self.torch.empty(self.n_local * mu, dtype=self.dtype, device=self.device))
+        xr, yr = self._blk[mu]
+        with self.torch.cuda.device(self.device):
+            xr.view(self.n_global, mu)[self.off:self.off + self.n_local].copy_(vin.t())  # column blocks -> row-major slab
+            if self.world > 1:
+                allgather_slabs_(xr, self.op.offs, self.op.sizes, mu, self.group)
+            self.op.engine.add_matrix_product_row_major("N", 1.0, xr, 0.0, yr, mu)
+            vout.copy_(yr.view(self.n_local, mu).t())
+
     # ---- reductions ---------------------------------------------------------------------------------------------
+    def allreduce_many(self, handles):
+        """one all-reduce for a list of small device results (the k x mu block of HPDDM_iterative.hpp:549); returns views"""
+        if self.world == 1 and not self.use_peer:
+            return handles
+        flat = self._allreduce(self.torch.cat([h.reshape(-1) for h in handles]))  # one dtype per call (all dots or all norms)
+        out, p = [], 0
+        for h in handles:
+            out.append(flat[p:p + h.numel()])
+            p += h.numel()
+        return out
+
     def _allreduce(self, t):
         if self.use_peer and t.numel() * (2 if t.is_complex() else 1) <= self.op.PEER_ALLREDUCE_MAX:
             return self.op.peer_allreduce_(t)
@@ -297,34 +456,34 @@ class CudaKrylovSpace:
             dist.all_reduce(self.torch.view_as_real(t) if t.is_complex() else t, group=self.group)
         return t
 
-    def dots(self, V, first, k, w):
+    def dots(self, V, first, k, w, reduce=True):
         h = self.torch.empty(k, dtype=self.dtype, device=self.device)
         self._reserve(k)
         _lib.check(self.lib.hmb200_krylov_dots(V.row(first).data_ptr(), V.n, k, w.data_ptr(), self.n_local, h.data_ptr(),
                                                self._scratch.data_ptr(), self.es, self._stream()))
         self.kernel_launches += 2
-        return self._allreduce(h)
+        return self._allreduce(h) if reduce else h
 
-    def combine(self, V, first, k, h, sign, w, want_norm):
+    def combine(self, V, first, k, h, sign, w, want_norm, reduce=True):
         n2 = self.torch.empty(1, dtype=self.torch.float64, device=self.device) if want_norm else None
         self._reserve(k)
         _lib.check(self.lib.hmb200_krylov_combine(V.row(first).data_ptr(), V.n, k, h.data_ptr(), float(sign), w.data_ptr(), self.n_local,
                                                   n2.data_ptr() if want_norm else None, self._scratch.data_ptr(), self.es, self._stream()))
         self.kernel_launches += 2 if want_norm else 1
-        return self._allreduce(n2) if want_norm else None
+        return (self._allreduce(n2) if reduce else n2) if want_norm else None
 
-    def axpby_norm(self, alpha, x, beta, y, out):
+    def axpby_norm(self, alpha, x, beta, y, out, reduce=True):
         n2 = self.torch.empty(1, dtype=self.torch.float64, device=self.device)
         self._reserve(1)
         a, b = complex(alpha), complex(beta)
         _lib.check(self.lib.hmb200_krylov_axpby((ctypes.c_double * 2)(a.real, a.imag), x.data_ptr(), (ctypes.c_double * 2)(b.real, b.imag), y.data_ptr(),
                                                 out.data_ptr(), self.n_local, n2.data_ptr(), self._scratch.data_ptr(), self.es, self._stream()))
         self.kernel_launches += 2
-        return self._allreduce(n2)
+        return self._allreduce(n2) if reduce else n2
 
-    def norm2(self, x):
+    def norm2(self, x, reduce=True):
         tmp = self.torch.empty_like(x)
-        return self.axpby_norm(1.0, x, 0.0, x, tmp)
+        return self.axpby_norm(1.0, x, 0.0, x, tmp, reduce=reduce)
 
     def scale(self, w, n2_dev):
         _lib.check(self.lib.hmb200_krylov_scale(w.data_ptr(), self.n_local, n2_dev.data_ptr(), self.es, self._stream()))
@@ -392,8 +551,10 @@ class B200Solver:
         return dict(self.infos)
 
     def solve(self, x, b, hpddm_args: str = ""):
-        """x (in/out, initial guess) and b in USER numbering; 1-D, or 2-D (n, mu) Fortran-ordered blocks solved column by
-        column.  x is updated IN PLACE like the reference (py::arg("x").noconvert())."""
+        """x (in/out, initial guess) and b in USER numbering; 1-D, or 2-D (n, mu) Fortran-ordered blocks, whose columns advance
+        in lockstep with one block operator call per iteration like HPDDM's GMRES with mu > 1 (`-hpddm_block_rhs columns`, an
+        option of this class only, solves them one after the other instead).  x is updated IN PLACE like the reference
+        (py::arg("x").noconvert())."""
         self.set_hpddm_args(hpddm_args)
         if str(self.opt.get("krylov_method", "gmres")).lower() not in ("gmres", "0"):
             raise NotImplementedError("only -hpddm_krylov_method gmres is on the accelerated path")
@@ -406,13 +567,19 @@ class B200Solver:
             raise TypeError("x must be a numpy array of the operator's dtype (it is updated in place)")
         t0 = time.perf_counter()
         its, calls = [], 0
-        cols = [(x_arr, b_arr)] if b_arr.ndim == 1 else [(x_arr[:, c], b_arr[:, c]) for c in range(b_arr.shape[1])]
-        for xc, bc in cols:
-            sol, it, info = gmres_driver(self.space, bc, xc, self.opt)
-            xc[...] = sol
-            its.append(it)
-            calls += info["operator_calls"]
-            self.last_info = info
+        lockstep = b_arr.ndim == 2 and b_arr.shape[1] > 1 and str(self.opt.get("block_rhs", "lockstep")).lower() != "columns"
+        if lockstep:  # HPDDM's GMRES with mu > 1: all columns advance together, one block operator call per iteration
+            sol, it, info = gmres_block_driver(self.space, b_arr, x_arr, self.opt)
+            x_arr[...] = sol
+            its, calls, self.last_info = [it], info["operator_calls"], info
+        else:
+            cols = [(x_arr, b_arr)] if b_arr.ndim == 1 else [(x_arr[:, c], b_arr[:, c]) for c in range(b_arr.shape[1])]
+            for xc, bc in cols:
+                sol, it, info = gmres_driver(self.space, bc, xc, self.opt)
+                xc[...] = sol
+                its.append(it)
+                calls += info["operator_calls"]
+                self.last_info = info
         self.infos.update({"Solve": str(time.perf_counter() - t0), "Nb_it": str(max(its)), "Nb_subdomains": str(getattr(self.space, "world", 1)),
                            "Precond": "None", "nb_mat_vec_prod": str(calls)})
         return max(its)

@@ -142,3 +142,67 @@ def gmres(matvec, b, x0=None, tol=1.0e-6, max_it=100, gmres_restart=40, orthogon
     if j != 0:
         _update_sol(x, H, V, s, abs(conv))
     return x, min(j, max_it), dict(operator_calls=calls, residuals=residuals, converged=(j <= max_it and j != 0) or j == 0)
+
+
+def gmres_block(matmat, B, X0=None, tol=1.0e-6, max_it=100, gmres_restart=40, orthogonalization="cgs", variant="right", **_ignored):
+    """IterativeMethod::GMRES for a block of mu right-hand sides (HPDDM_GMRES.hpp:30-196 with mu > 1): mu independent GMRES
+    recurrences advanced in LOCKSTEP -- one operator call (GMV on the n x mu block) per iteration, one Hessenberg matrix,
+    rotation set and `hasConverged` entry per column; the loop ends when no column is left at the sentinel (:147-150), and
+    updateSol uses each column's own dimension |hasConverged[nu]| (computeMin / addSol, HPDDM_iterative.hpp:283-326).
+    matmat(X) -> A X on (n, mu) arrays.  Returns (X, iterations, info); info["converged_at"] = the per-column hasConverged."""
+    B = np.asarray(B)
+    dt = np.complex128 if np.iscomplexobj(B) else np.float64
+    B = B.astype(dt)
+    n, mu = B.shape
+    X = np.zeros((n, mu), dt) if X0 is None else np.array(X0, dtype=dt)
+    m = min(gmres_restart, max_it)
+    H = [[np.zeros(m + 1, dt) for _ in range(m)] for _ in range(mu)]
+    V = np.zeros((mu, m + 1, n), dt)  # V[nu][i] = column nu of the i-th block of the basis
+    s = np.zeros((mu, m + 1), dt)
+    sn = np.zeros((mu, m))
+    norm_b = np.sqrt(np.einsum("ij,ij->j", B.conj(), B).real)
+    norm_b[norm_b < HPDDM_EPS] = 1.0
+    calls = 0
+    conv = [-m] * mu
+    j = 1
+    while j <= max_it:
+        R = B - matmat(X)
+        calls += 1
+        beta2 = np.einsum("ij,ij->j", R.conj(), R).real
+        if j == 1 and np.any(beta2 < np.finfo(np.float64).eps ** 2):  # :87-90, any column
+            j = 0
+            conv = [0] * mu
+            break
+        for nu in range(mu):
+            if conv[nu] > 0:
+                conv[nu] = 0
+            s[nu, 0] = np.sqrt(beta2[nu])
+            V[nu, 0] = R[:, nu] / s[nu, 0]
+        i = 0
+        while i < m and j <= max_it:
+            W = matmat(np.ascontiguousarray(V[:, i, :].T))
+            calls += 1
+            for nu in range(mu):
+                V[nu, i + 1] = W[:, nu]
+                _arnoldi(H[nu], V[nu], s[nu], sn[nu], i, m, orthogonalization)
+            i += 1
+            for nu in range(mu):
+                r = abs(s[nu, i])
+                if conv[nu] == -m and ((tol > 0 and r / norm_b[nu] <= tol) or (tol < 0 and r <= -tol)):
+                    conv[nu] = i
+            if -m not in conv:
+                i = 0
+                break
+            j += 1
+        if j != max_it + 1 and i == m:
+            for nu in range(mu):
+                _update_sol(X[:, nu], H[nu], V[nu], s[nu], abs(conv[nu]))
+        else:
+            break
+    if j == max_it + 1 and m > 0:
+        rem = max_it % m
+        conv = [(rem if rem > 0 else -c) if c < 0 else c for c in conv]
+    if j != 0:
+        for nu in range(mu):
+            _update_sol(X[:, nu], H[nu], V[nu], s[nu], abs(conv[nu]))
+    return X, min(j, max_it), dict(operator_calls=calls, converged_at=list(conv), converged=(j <= max_it))

@@ -30,6 +30,36 @@ class NumpyKrylovSpace:
     def basis(self, count):
         return _Basis(np.zeros((count, self.n_local), self.np_dtype), self.n_local)
 
+    def block(self, mu):
+        return np.zeros((mu, self.n_local), self.np_dtype)
+
+    def block_basis(self, count, mu):
+        from htool_python_b200.solver import _BlockBasis
+
+        return _BlockBasis(np.zeros((count, mu, self.n_local), self.np_dtype))
+
+    def set_block_from_user(self, blk, host):
+        for c in range(blk.shape[0]):
+            self.set_from_user(blk[c], np.asarray(host)[:, c])
+
+    def get_block_to_user(self, blk):
+        return np.asfortranarray(np.stack([self.get_to_user(blk[c]) for c in range(blk.shape[0])], axis=1))
+
+    def matmat(self, vin, vout):
+        mu = vin.shape[0]
+        xr = np.ascontiguousarray(np.stack([self._gather(vin[c]).copy() for c in range(mu)], axis=1))  # row-major n_global x mu
+        yr = np.zeros((self.n_local, mu), self.np_dtype)
+        self.fo.add_matrix_product_row_major(self.flat, "N", 1.0, xr, 0.0, yr, mu)
+        vout[:] = yr.T
+
+    def allreduce_many(self, handles):
+        flat = self._allreduce(np.concatenate([np.asarray(h).reshape(-1) for h in handles]))
+        out, p = [], 0
+        for h in handles:
+            out.append(flat[p:p + np.size(h)])
+            p += np.size(h)
+        return out
+
     def set_from_user(self, vec, host):
         vec[:] = np.asarray(host, dtype=self.np_dtype)[self.perm][self.off:self.off + self.n_local]
 
@@ -61,19 +91,25 @@ class NumpyKrylovSpace:
             dist.all_reduce(t)
         return a
 
-    def dots(self, V, first, k, w):
-        return self._allreduce(np.ascontiguousarray(V.data[first:first + k].conj() @ w))
+    def dots(self, V, first, k, w, reduce=True):
+        h = np.ascontiguousarray(V.data[first:first + k].conj() @ w)
+        return self._allreduce(h) if reduce else h
 
-    def combine(self, V, first, k, h, sign, w, want_norm):
+    def combine(self, V, first, k, h, sign, w, want_norm, reduce=True):
         w += sign * (h @ V.data[first:first + k])
-        return self._allreduce(np.array([np.vdot(w, w).real])) if want_norm else None
+        if not want_norm:
+            return None
+        n2 = np.array([np.vdot(w, w).real])
+        return self._allreduce(n2) if reduce else n2
 
-    def axpby_norm(self, alpha, x, beta, y, out):
+    def axpby_norm(self, alpha, x, beta, y, out, reduce=True):
         out[:] = alpha * x + beta * y
-        return self._allreduce(np.array([np.vdot(out, out).real]))
+        n2 = np.array([np.vdot(out, out).real])
+        return self._allreduce(n2) if reduce else n2
 
-    def norm2(self, x):
-        return self._allreduce(np.array([np.vdot(x, x).real]))
+    def norm2(self, x, reduce=True):
+        n2 = np.array([np.vdot(x, x).real])
+        return self._allreduce(n2) if reduce else n2
 
     def scale(self, w, n2):
         w /= np.sqrt(n2[0])

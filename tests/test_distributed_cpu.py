@@ -128,8 +128,13 @@ def _gmres_worker(rank, world, port, n, q):
         it = solver.solve(x, b, args)
         # every rank must hold the same solution and iteration count; compare with the one-process oracle GMRES whose
         # operator is the concatenation of the same slabs
+        # a block of 3 right-hand sides in lockstep (one row-major block product + one all-reduce of all columns per step)
+        B = np.asfortranarray(rng.random((n, 3)))
+        XB = np.zeros_like(B, order="F")
+        itB = solver.solve(XB, B, args)
+        callsB = solver.last_info["operator_calls"]
         slabs = [None] * world
-        dist.all_gather_object(slabs, (it, x))
+        dist.all_gather_object(slabs, (it, x, itB, XB))
         if rank == 0:
             ps, pt = slab.source_permutation, slab.target_permutation
             flats = [slab] + [FlatHMatrix.from_htool(bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-6, eta=10.0, target_partition_number=p, partition_number_for_symmetry=p)) for p in range(1, world)]
@@ -145,7 +150,10 @@ def _gmres_worker(rank, world, port, n, q):
 
             x_ref, it_ref, info = go.gmres(matvec, b, **go.parse_hpddm_args(args))
             same = all(s[0] == it and np.array_equal(s[1], x) for s in slabs)
-            q.put(("ok", (it, it_ref, same, rel_err(x, x_ref), np.linalg.norm(matvec(x) - b) / np.linalg.norm(b))))
+            XB_ref, itB_ref, infoB = go.gmres_block(lambda Y: np.stack([matvec(Y[:, c]) for c in range(Y.shape[1])], axis=1), B, **go.parse_hpddm_args(args))
+            sameB = all(s[2] == itB and np.array_equal(s[3], XB) for s in slabs)
+            q.put(("ok", (it, it_ref, same and sameB, rel_err(x, x_ref), np.linalg.norm(matvec(x) - b) / np.linalg.norm(b),
+                          (itB, callsB), (itB_ref, infoB["operator_calls"]), rel_err(XB, XB_ref))))
     except Exception:  # pragma: no cover
         import traceback
 
@@ -168,7 +176,8 @@ def test_distributed_gmres_two_ranks_gloo():
     for p in procs:
         p.join(timeout=120)
     assert status == "ok", res
-    it, it_ref, same, err, resid = res
+    it, it_ref, same, err, resid, block, block_ref, err_block = res
     assert it == it_ref and 0 < it < 150, (it, it_ref)
     assert same
     assert err < 1e-7 and resid < 2e-6, (err, resid)
+    assert block == block_ref and err_block < 1e-7, (block, block_ref, err_block)

@@ -296,7 +296,14 @@ def _dist_worker(rank, world, port, q, kernel="laplace_reg"):
         xs = np.zeros(n, dt)
         it = B200Solver(op).solve(xs, b, args)
         x_ref, it_ref, _ = go.gmres(matvec, b, **go.parse_hpddm_args(args))
-        q.put((rank, rel_err(y, y_ref), rel_err(Y, Y_ref), bool(Y.flags.f_contiguous), bool(op.fused), same, status, it, it_ref, rel_err(xs, x_ref), et))
+        # a block of 3 right-hand sides in lockstep on the multi-RHS product (row-major all-gather of the block over NCCL)
+        B = np.asfortranarray(helpers.rand_vec(rng, n, dt, 3))
+        XB = np.zeros_like(B, order="F")
+        sb = B200Solver(op)
+        itB = sb.solve(XB, B, args)
+        XB_ref, itB_ref, infoB = go.gmres_block(lambda Z: np.stack([matvec(Z[:, c]) for c in range(Z.shape[1])], axis=1), B, **go.parse_hpddm_args(args))
+        blk = (itB, sb.last_info["operator_calls"], itB_ref, infoB["operator_calls"], rel_err(XB, XB_ref))
+        q.put((rank, rel_err(y, y_ref), rel_err(Y, Y_ref), bool(Y.flags.f_contiguous), bool(op.fused), same, status, it, it_ref, rel_err(xs, x_ref), et, blk))
         op_nccl.close()
         op.close()
     finally:
@@ -327,7 +334,8 @@ def test_distributed_operator(world, kernel):
     res = [q.get(timeout=300) for _ in range(world)]
     for p in procs:
         p.join(timeout=120)
-    for rank, e1, e2, f_order, fused, same, status, it, it_ref, ex, et in res:
+    for rank, e1, e2, f_order, fused, same, status, it, it_ref, ex, et, blk in res:
+        assert blk[0] == blk[2] and blk[1] == blk[3] and 0 < blk[0] < 100 and blk[4] < 1e-7, (rank, blk)
         assert e1 < TOL and e2 < TOL and et < TOL and f_order, (rank, e1, e2, et)
         assert same and status == 0, (rank, same, status)
         assert fused == (world > 1), "the fused all-gather must be the path that runs on several GPUs"

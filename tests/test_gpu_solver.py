@@ -8,7 +8,7 @@ import pytest
 
 import helpers
 from helpers import rel_err
-from test_gmres_oracle import X_TOL, check_solution, gmres_golden
+from test_gmres_oracle import X_TOL, check_block_solution, check_solution, gmres_block_golden, gmres_golden
 
 pytestmark = pytest.mark.gpu
 
@@ -122,4 +122,25 @@ def test_device_gmres_over_peer_collectives_single_rank(case):
         for _ in range(3):
             op.peer_allreduce_(t)
         assert torch.equal(torch.view_as_real(t) if t.is_complex() else t, torch.view_as_real(ref) if ref.is_complex() else ref)
+    op.close()
+
+
+@pytest.mark.parametrize("peer", [False, True])
+@pytest.mark.parametrize("case", range(4))
+def test_device_block_gmres_matches_reference_hpddm(case, peer):
+    """blocks of right-hand sides: the lockstep GMRES on the multi-RHS DMMA product == the reference's HPDDM GMRES called with
+    mu > 1 (tests/golden/gmres_block_golden.npz): iteration count and number of block operator calls EQUAL, every column's
+    iterate within a fraction of the tolerance; `peer` routes the small reductions through the peer-memory all-reduce."""
+    from htool_python_b200 import B200DistributedOperator, B200Solver
+
+    g = gmres_block_golden()[case]
+    flat, _ = helpers.load_golden(g["fixture"])
+    op = B200DistributedOperator(flat, [(0, flat.n_rows)], fused_allgather=peer)
+    solver = B200Solver(op)
+    X = np.zeros_like(g["B"], order="F")
+    it = solver.solve(X, g["B"], g["args"])
+    assert it == g["iterations"] and solver.last_info["operator_calls"] == g["calls"], (it, solver.last_info["operator_calls"])
+    check_block_solution(flat, g, X, case, scale=10.0)
+    if peer:
+        assert op.peer_status() == 0
     op.close()
