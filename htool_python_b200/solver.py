@@ -213,7 +213,10 @@ def gmres_block_driver(sp, B_host, X_host, opt: dict):
     VB = sp.block_basis(m + 1, mu)
     hess = [_Hessenberg(m, sp.np_dtype) for _ in cols]
     conv = [-m] * mu
-    calls, residuals = 0, []
+    calls, residuals, unused = 0, [], 0
+    speculate = bool(opt.get("speculate", True)) and hasattr(sp, "host_begin")
+    if not hasattr(sp, "host_begin"):
+        sp.host_begin, sp.host_end = (lambda handles: handles), (lambda token: sp.host(token))
 
     def update(dims):
         for c in cols:
@@ -236,9 +239,12 @@ def gmres_block_driver(sp, B_host, X_host, opt: dict):
             hess[c].start(math.sqrt(beta2[c]))
             sp.scale(V0[c], beta2_dev[c])
         i = 0
+        launched = False  # the block product of step i was already enqueued (speculatively) by step i-1
         while i < m and j <= max_it:
             W = VB.block(i + 1)
-            sp.matmat(VB.block(i), W)
+            if not launched:
+                sp.matmat(VB.block(i), W)
+            launched = False
             calls += 1
             if mgs:  # HPDDM_iterative.hpp:522-540: one reduction of mu values per basis vector
                 hk_all = []
@@ -247,16 +253,19 @@ def gmres_block_driver(sp, B_host, X_host, opt: dict):
                     n2_raw = [sp.combine(VB.col(c), k, 1, hk[c], -1.0, W[c], want_norm=(k == i), reduce=False) for c in cols]
                     hk_all.append(hk)
                 n2_dev = sp.allreduce_many(n2_raw)
-                got = sp.host([hk_all[k][c] for c in cols for k in range(i + 1)] + n2_dev)
-                hcols = [np.array([got[c * (i + 1) + k][0] for k in range(i + 1)]) for c in cols]
+                token = sp.host_begin([hk_all[k][c] for c in cols for k in range(i + 1)] + n2_dev)
             else:  # classical Gram-Schmidt (:541-552)
                 h_dev = sp.allreduce_many([sp.dots(VB.col(c), 0, i + 1, W[c], reduce=False) for c in cols])
                 n2_dev = sp.allreduce_many([sp.combine(VB.col(c), 0, i + 1, h_dev[c], -1.0, W[c], want_norm=True, reduce=False) for c in cols])
-                got = sp.host(h_dev + n2_dev)
-                hcols = got[:mu]
+                token = sp.host_begin(h_dev + n2_dev)
             if i < m - 1:
                 for c in cols:
                     sp.scale(W[c], n2_dev[c])
+                if speculate and j + 1 <= max_it:  # next block product enqueued before the host reads the Hessenberg columns
+                    sp.matmat(W, VB.block(i + 2))
+                    launched = True
+            got = sp.host_end(token)
+            hcols = [np.array([got[c * (i + 1) + k][0] for k in range(i + 1)]) for c in cols] if mgs else got[:mu]
             res = [hess[c].push(i, hcols[c], real0(got[len(got) - mu + c])) for c in cols]
             i += 1
             residuals.append([res[c] / norm_b[c] for c in cols])
@@ -265,6 +274,7 @@ def gmres_block_driver(sp, B_host, X_host, opt: dict):
                     conv[c] = i
             if -m not in conv:
                 i = 0
+                unused += int(launched)
                 break
             j += 1
         if j != max_it + 1 and i == m:  # restart
@@ -278,7 +288,7 @@ def gmres_block_driver(sp, B_host, X_host, opt: dict):
         update([abs(c) for c in conv])
     it = min(j, max_it)
     return sp.get_block_to_user(x), it, dict(operator_calls=calls, residuals=residuals, converged=bool(j <= max_it), norm_b=norm_b,
-                                            converged_at=list(conv), speculative_unused=0, block=mu)
+                                            converged_at=list(conv), speculative_unused=unused, block=mu)
 
 
 class _Basis:
