@@ -342,6 +342,7 @@ class CudaKrylovSpace:
         self._hpin, self._hev = None, None
         self._k_max = 0
         self._blk = {}
+        self.mm_min_cols = 5  # narrowest block that goes through the multi-RHS (DMMA) product, see matmat
         self.kernel_launches = 0
 
     # ---- storage ------------------------------------------------------------------------------------------------
@@ -434,6 +435,13 @@ class CudaKrylovSpace:
         from .distributed import allgather_slabs_
 
         mu = int(vin.shape[0])
+        if mu < self.mm_min_cols:
+            # a pass of the DMMA kernel costs about the same for 2 as for 32 right-hand sides (profiles/r01_block_gmres_profile.log:
+            # ~10 ms at N=1M against 2.4 ms for the single-RHS stream kernel), so very narrow blocks take the streamed product
+            # per column (same values to rounding, same number of block operator calls)
+            for c in range(mu):
+                self.matvec(vin[c], vout[c])
+            return
         if mu not in self._blk:
             self._blk[mu] = (self.torch.empty(self.n_global * mu, dtype=self.dtype, device=self.device),
                              self.torch.empty(self.n_local * mu, dtype=self.dtype, device=self.device))

@@ -300,6 +300,7 @@ def _dist_worker(rank, world, port, q, kernel="laplace_reg"):
         B = np.asfortranarray(helpers.rand_vec(rng, n, dt, 3))
         XB = np.zeros_like(B, order="F")
         sb = B200Solver(op)
+        sb.space.mm_min_cols = 0  # force the multi-RHS product (3 columns would otherwise take the streamed product per column)
         itB = sb.solve(XB, B, args)
         XB_ref, itB_ref, infoB = go.gmres_block(lambda Z: np.stack([matvec(Z[:, c]) for c in range(Z.shape[1])], axis=1), B, **go.parse_hpddm_args(args))
         blk = (itB, sb.last_info["operator_calls"], itB_ref, infoB["operator_calls"], rel_err(XB, XB_ref))

@@ -125,18 +125,22 @@ def test_device_gmres_over_peer_collectives_single_rank(case):
     op.close()
 
 
+@pytest.mark.parametrize("product", ["dmma", "auto"])
 @pytest.mark.parametrize("peer", [False, True])
 @pytest.mark.parametrize("case", range(4))
-def test_device_block_gmres_matches_reference_hpddm(case, peer):
+def test_device_block_gmres_matches_reference_hpddm(case, peer, product):
     """blocks of right-hand sides: the lockstep GMRES on the multi-RHS DMMA product == the reference's HPDDM GMRES called with
     mu > 1 (tests/golden/gmres_block_golden.npz): iteration count and number of block operator calls EQUAL, every column's
-    iterate within a fraction of the tolerance; `peer` routes the small reductions through the peer-memory all-reduce."""
+    iterate within a fraction of the tolerance; `peer` routes the small reductions through the peer-memory all-reduce;
+    `product`: "dmma" forces the multi-RHS kernel, "auto" lets these narrow blocks take the streamed product per column."""
     from htool_python_b200 import B200DistributedOperator, B200Solver
 
     g = gmres_block_golden()[case]
     flat, _ = helpers.load_golden(g["fixture"])
     op = B200DistributedOperator(flat, [(0, flat.n_rows)], fused_allgather=peer)
     solver = B200Solver(op)
+    if product == "dmma":
+        solver.space.mm_min_cols = 0
     X = np.zeros_like(g["B"], order="F")
     it = solver.solve(X, g["B"], g["args"])
     assert it == g["iterations"] and solver.last_info["operator_calls"] == g["calls"], (it, solver.last_info["operator_calls"])
