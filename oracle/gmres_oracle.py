@@ -2,7 +2,8 @@
 
 Plain-numpy restatement of the Krylov solver the reference's DDM::solve runs
 (lib/htool/include/htool/solvers/ddm.hpp:193 -> HPDDM::IterativeMethod::solve -> IterativeMethod::GMRES,
-lib/hpddm/include/HPDDM_GMRES.hpp:30-196), for ONE right-hand side, no preconditioner
+lib/hpddm/include/HPDDM_GMRES.hpp:30-196), for ONE right-hand side (`gmres`) and for a block of mu right-hand sides
+advanced in lockstep as HPDDM does with mu > 1 (`gmres_block`), no preconditioner
 (-hpddm_schwarz_method none, ddm.hpp:136-138: with M = I the left/right variants coincide), restarted GMRES(m) with the
 classical (default) or modified Gram-Schmidt of IterativeMethod::orthogonalization (HPDDM_iterative.hpp:512-560) and the
 Givens-rotation least-squares update of IterativeMethod::Arnoldi (HPDDM_iterative.hpp:722-768), solution update
@@ -10,8 +11,8 @@ IterativeMethod::updateSol / computeMin / addSol (HPDDM_iterative.hpp:276-330).
 
 PARITY PINNED: tests/test_gmres_oracle.py checks this restatement against the reference's own HPDDM code compiled from
 /root/reference (oracle/_ref/libhpddm_ref.so, oracle/hpddm_ref.cpp): same iteration counts, same number of operator calls,
-iterates equal to ~1e-12, on real/complex dense systems and on the reference's solver fixture
-(lib/htool_generate_data_test/data/output_*/{matrix,rhs,sol}.bin).
+iterates equal to ~1e-12, on real/complex dense systems (single and block right-hand sides) and on the reference's solver
+fixture (lib/htool_generate_data_test/data/output_*/{matrix,rhs,sol}.bin).
 """
 import numpy as np
 
