@@ -60,6 +60,42 @@ def allgather_slabs_(buf, offs: List[int], sizes: List[int], mu: int, group=None
     return buf
 
 
+def exchange_sum_slabs_(full, offs: List[int], sizes: List[int], out_local, beta=0.0, group=None):
+    """out_local = beta * out_local + sum over the ranks r (ascending) of full_r[offs[me] : offs[me] + sizes[me]], where
+    `full_r` is rank r's full-length contribution: the exchange step of the TRANSPOSED local-to-local product
+    (add_distributed_operator_vector_product_local_to_local.hpp:60-87: MPI_Alltoallv of the slabs, scal by beta, then one axpy
+    per rank in rank order).  Point-to-point sends / receives (both NCCL and gloo have them), summed in rank order so that the
+    result does not depend on arrival order."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    mine = full[offs[rank]:offs[rank] + sizes[rank]]
+    if beta == 0:
+        out_local.zero_()
+    else:
+        out_local.mul_(beta)
+    if world == 1:
+        out_local.add_(mine)
+        return out_local
+    rbuf = torch.empty((world, sizes[rank]), dtype=full.dtype, device=full.device)
+    peer = lambda q: dist.get_global_rank(group, q) if group is not None else q  # noqa: E731
+    ops = []
+    for q in range(world):
+        if q == rank:
+            continue
+        if sizes[q]:
+            ops.append(dist.P2POp(dist.isend, full[offs[q]:offs[q] + sizes[q]].contiguous(), peer(q), group))
+        if sizes[rank]:
+            ops.append(dist.P2POp(dist.irecv, rbuf[q], peer(q), group))
+    for req in (dist.batch_isend_irecv(ops) if ops else []):
+        req.wait()
+    for q in range(world):
+        out_local.add_(mine if q == rank else rbuf[q])
+    return out_local
+
+
 class _RawDeviceArray:
     """`__cuda_array_interface__` view of device memory owned by libhmb200.so (wrapped by torch.as_tensor without a copy)"""
 
@@ -254,6 +290,32 @@ class B200DistributedOperator:
 
             dist.all_reduce(torch.view_as_real(y_cluster) if y_cluster.is_complex() else y_cluster, group=self.group)
         return y_cluster
+
+    def matvec_local_to_local_(self, x_local, y_local, trans: str = "N", alpha=1.0, beta=0.0):
+        """y_local = beta y_local + alpha op(A) x on LOCAL slabs (device tensors, cluster numbering): the solver-side driver
+        internal_add_distributed_operator_vector_product_local_to_local (…vector_product_local_to_local.hpp:19-89).
+        'N': all-gather of the input slabs (:44), then the rank's global-to-local product.  'T' / 'C': op(A_p) applied to the
+        rank's slab gives a full-length contribution; the slabs are exchanged and summed in rank order (:60-87).  Square
+        operators with one partition for both sides (what the solver uses); 'T'/'C' need build_transpose=1."""
+        import torch
+
+        if self.n_target != self.n_source:
+            raise RuntimeError("the local-to-local driver needs a square operator")
+        o, s = self.offs[self.rank], self.sizes[self.rank]
+        if trans == "N":
+            if self.fused:
+                xg = self.peer_allgather_(x_local)
+            else:
+                xg = self._buffers(1)[0][1]
+                xg[o:o + s].copy_(x_local)
+                allgather_slabs_(xg, self.offs, self.sizes, 1, self.group)
+            self.engine.add_vector_product("N", alpha, xg, beta, y_local)
+            return y_local
+        if trans not in ("T", "C"):
+            raise ValueError("trans must be 'N', 'T' or 'C'")
+        full = self._buffers(1)[0][2]
+        self.engine.add_vector_product(trans, alpha, x_local, 0.0, full)
+        return exchange_sum_slabs_(full, self.offs, self.sizes, y_local, beta, self.group if torch.distributed.is_initialized() else None)
 
     def matmat_cluster_(self, X_cluster, Y_cluster, mu: int):
         """row-major (n x mu) blocks (add_distributed_operator_matrix_product_row_major_global_to_global.hpp:18-84)."""

@@ -56,6 +56,27 @@ def _worker(rank, world, port, kernel, n, mu, q):
         allgather_slabs_(Yc, offs, sizes, mu)                           # MPI_Allgatherv (:76)
         Y = np.empty((n, mu), dtype=dt)
         Y[slab.target_permutation] = Yc.view(n, mu).numpy()             # root_cluster_to_global (:117)
+        # transposed local-to-local driver (…vector_product_local_to_local.hpp:60-87): op(A_p) x_p is a full-length
+        # contribution; slabs exchanged point-to-point and summed in rank order on top of beta * out
+        from htool_python_b200.distributed import exchange_sum_slabs_
+
+        for tr in ["T"] + (["C"] if dt == np.complex128 else []):
+            x_loc = helpers.rand_vec(np.random.default_rng(100 + rank), sizes[rank], dt)
+            contrib = np.zeros(n, dt)
+            fo.add_vector_product(slab, tr, 1.5, x_loc, 0.0, contrib)
+            out0 = helpers.rand_vec(np.random.default_rng(200 + rank), sizes[rank], dt)
+            beta = 0.5
+            out_t = torch.from_numpy(out0.copy())
+            exchange_sum_slabs_(torch.from_numpy(contrib), offs, sizes, out_t, beta)
+            everyone = [None] * world
+            dist.all_gather_object(everyone, contrib)
+            expect = beta * out0
+            for r in range(world):
+                expect = expect + everyone[r][offs[rank]:offs[rank] + sizes[rank]]
+            assert np.array_equal(out_t.numpy(), expect), tr
+            out_z = torch.from_numpy(np.full(sizes[rank], np.nan).astype(dt))
+            exchange_sum_slabs_(torch.from_numpy(contrib), offs, sizes, out_z, 0.0)   # beta = 0 must not read `out`
+            assert np.array_equal(out_z.numpy(), expect - beta * out0 + 0) or rel_err(out_z.numpy(), expect - beta * out0) < 1e-13
         if rank == 0:
             # the same operator assembled in one piece by the reference, product by the oracle in user numbering
             tree1 = bridge.create_cluster_tree(pts, 2, 1, 32)

@@ -343,6 +343,78 @@ def test_distributed_operator(world, kernel):
         assert it == it_ref and 0 < it < 100 and ex < 1e-7, (rank, it, it_ref, ex)
 
 
+def _l2l_worker(rank, world, port, q):
+    """local-to-local drivers on 2 GPUs: 'N' (input all-gather + slab product) and 'T' (slab exchange, rank-ordered sum)"""
+    import os
+
+    import torch
+    import torch.distributed as dist
+
+    from htool_python_b200 import B200DistributedOperator, FlatHMatrix, bridge
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(21)
+        n = 5000
+        g = rng.standard_normal((3, n))
+        pts = np.asfortranarray(g / np.linalg.norm(g, axis=0))
+        tree = bridge.create_cluster_tree(pts, 2, world, 32)
+        build = lambda p: bridge.build_hmatrix("laplace_reg", tree, epsilon=1e-5, eta=10.0, target_partition_number=p, partition_number_for_symmetry=p)  # noqa: E731
+        flats = [FlatHMatrix.from_htool(build(p)) for p in range(world)]
+        op = B200DistributedOperator(flats[rank], tree.partition, fused_allgather=False, build_transpose=1)
+        offs, sizes = op.offs, op.sizes
+        xg = rng.random(n)                                      # cluster numbering, the same on every rank
+        dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(op.device)  # noqa: E731
+        errs = []
+        for tr in ("N", "T"):
+            y0 = rng.random(n)
+            y_loc = dev(y0[offs[rank]:offs[rank] + sizes[rank]])
+            op.matvec_local_to_local_(dev(xg[offs[rank]:offs[rank] + sizes[rank]]), y_loc, tr, 1.25, -0.5)
+            ref = -0.5 * y0
+            for p, f in enumerate(flats):
+                if tr == "N":
+                    part = np.zeros(sizes[p])
+                    fo.add_vector_product(f, "N", 1.25, xg, 0.0, part)
+                    ref[offs[p]:offs[p] + sizes[p]] += part
+                else:
+                    part = np.zeros(n)
+                    fo.add_vector_product(f, "T", 1.25, np.ascontiguousarray(xg[offs[p]:offs[p] + sizes[p]]), 0.0, part)
+                    ref += part
+            errs.append(rel_err(y_loc.cpu().numpy(), ref[offs[rank]:offs[rank] + sizes[rank]]))
+        q.put((rank, errs))
+        op.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(not helpers.bridge_available(), reason="bridge not built")
+def test_local_to_local_drivers_two_gpus():
+    """B200DistributedOperator.matvec_local_to_local_ ('N' and the transposed exchange) vs the restated driver on the oracle"""
+    import socket
+
+    import torch
+    import torch.multiprocessing as mp
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_l2l_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(2)]
+    for p in procs:
+        p.join(timeout=120)
+    for rank, errs in res:
+        assert max(errs) < TOL, (rank, errs)
+
+
 @pytest.mark.parametrize("name,mu", [("d_N_cylinder", 64), ("d_N_rect", 70), ("d_SL_cylinder", 17), ("z_N_sphere", 32), ("z_HL_cylinder", 40), ("z_SL_sphere", 5)])
 def test_multi_rhs_dmma(name, mu):
     """Y = beta*Y + alpha*op(A)*X on the DMMA kernels (several passes, padded column tails) vs the oracle, and the
