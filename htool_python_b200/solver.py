@@ -554,7 +554,7 @@ class CudaKrylovSpace:
 class B200Solver:
     """Drop-in for the solve surface of the reference's `Htool.Solver` / `ComplexSolver` (`solve(x, b, hpddm_args)`,
     `set_hpddm_args`, `get_information`; src/htool/solver/solver.hpp:23-64) for the unpreconditioned GMRES path, on a
-    `B200DistributedOperator` (or a `B200HMatrix`-style single-process operator wrapped by `from_hmatrix`)."""
+    `B200DistributedOperator` (a single-process `B200HMatrix` is wrapped with `B200DistributedOperator.from_engine(h.engine, flat)`)."""
 
     def __init__(self, distributed_operator, space=None):
         self.op = distributed_operator
