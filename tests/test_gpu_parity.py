@@ -343,6 +343,28 @@ def test_distributed_operator(world, kernel):
         assert it == it_ref and 0 < it < 100 and ex < 1e-7, (rank, it, it_ref, ex)
 
 
+@pytest.mark.parametrize("name", ["d_N_cylinder", "z_N_sphere"])
+def test_local_to_local_driver_single_rank(name):
+    """matvec_local_to_local_ with one rank: 'N' and the transposed branches (alpha, beta) vs the oracle"""
+    import torch
+
+    from htool_python_b200 import B200DistributedOperator
+
+    flat, _ = load_golden(name)
+    n = flat.n_rows
+    op = B200DistributedOperator(flat, [(0, n)], fused_allgather=False, build_transpose=1)
+    rng = np.random.default_rng(0)
+    alpha, beta = (1.25, -0.5)
+    for tr in ["N", "T"] + (["C"] if flat.dtype == "z" else []):
+        x, y0 = helpers.rand_vec(rng, n, flat.np_dtype), helpers.rand_vec(rng, n, flat.np_dtype)
+        y = torch.from_numpy(y0.copy()).to(op.device)
+        op.matvec_local_to_local_(torch.from_numpy(x).to(op.device), y, tr, alpha, beta)
+        ref = y0.copy()
+        fo.add_vector_product(flat, tr, alpha, x, beta, ref)
+        assert rel_err(y.cpu().numpy(), ref) < TOL, tr
+    op.close()
+
+
 def _l2l_worker(rank, world, port, q):
     """local-to-local drivers on 2 GPUs: 'N' (input all-gather + slab product) and 'T' (slab exchange, rank-ordered sum)"""
     import os
