@@ -4,6 +4,7 @@
 #include "planner.h"
 #include "../kernels/stream_kernels.cuh"
 #include "../kernels/mm_kernels.cuh"
+#include "../kernels/mmf_kernels.cuh"
 #include "../kernels/peer_kernels.cuh"
 
 #include <chrono>
@@ -577,6 +578,26 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
     return 0;
 }
 
+// ---- EXPERIMENTAL (Options.mm_variant bit 2): the DFMA consumer of mmf_kernels.cuh, one instantiation per pass width ----
+template <typename T>
+int mmf_ncol(int nc) {
+    const int nc8 = (nc + 7) & ~7;
+    if (nc8 <= 8) return 8;
+    if (nc8 <= 16 || sizeof(T) == 16) return 16;
+    return 32;
+}
+template <typename T, int PHASE>
+void launch_mmf(int ncol, unsigned grid, int threads, size_t smem, cudaStream_t st, const MmParams &p) {
+    auto go = [&](auto kern) {
+        CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, threads, smem, st>>>(p);
+    };
+    if (ncol == 8) go(hmatrix_mmf_kernel<T, PHASE, 8>);
+    else if (ncol == 16) go(hmatrix_mmf_kernel<T, PHASE, 16>);
+    else if constexpr (sizeof(T) == 8) go(hmatrix_mmf_kernel<T, PHASE, 32>);
+    else throw std::runtime_error("mmf: complex passes hold at most 16 columns");
+}
+
 // ---- multi-RHS on the DMMA kernels ------------------------------------------------------------------------------
 // Y(:, c0:c0+nc) = beta*Y + alpha*op(A)*X(:, c0:c0+nc) for every pass of <= 64 (32 complex) columns.
 //   x: device; row-major n_in x mu (perm_in == nullptr), or COLUMN-major user block gathered through perm_in
@@ -584,7 +605,8 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
 template <typename T>
 void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, const T *x, const int32_t *perm_in, T *y, int mu) {
     const Options &o = h->opt;
-    const int PC = mm_pass_cols<T>();
+    const bool dfma = (o.mm_variant & 4) != 0; // experimental DFMA consumer (mmf_kernels.cuh): passes of <= 32 (16 complex) columns
+    const int PC = dfma ? mmf_pass_cols<T>() : mm_pass_cols<T>();
     const int threads = (kMmConsumerWarps + 1) * 32;
     const int ctas = o.ctas > 0 ? o.ctas : h->n_sms;
     for (int c0 = 0; c0 < mu; c0 += PC) {
@@ -619,7 +641,10 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
             p.stream = po.stream[2]; p.stages = po.stages[2]; p.zcopies = po.zcopies[2]; p.units = po.units[2];
             p.n_units = po.n_units[2]; p.n_zcopies = 0; p.counter = h->counters; p.stage_bytes = o.mm_stage_bytes;
             size_t smem = mm_smem_bytes(1, h->es, o.mm_stage_bytes, 0, 2, o.mm_bin_cols, ld);
-            (o.mm_variant & 1 ? hmatrix_mm_kernel<T, 1, true> : hmatrix_mm_kernel<T, 1, false>)<<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[2]), threads, smem, h->stream>>>(p);
+            const unsigned grid1 = (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[2]);
+            if (dfma) launch_mmf<T, 1>(mmf_ncol<T>(nc), grid1, threads, mmf_smem_bytes(1, h->es, o.mm_stage_bytes, 0, 2, o.mm_bin_cols, ld), h->stream, p);
+            else
+            (o.mm_variant & 1 ? hmatrix_mm_kernel<T, 1, true> : hmatrix_mm_kernel<T, 1, false>)<<<grid1, threads, smem, h->stream>>>(p);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[1], h->stream));
@@ -633,7 +658,10 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
             p.stream = po.stream[1]; p.stages = po.stages[1]; p.zcopies = po.zcopies[1]; p.units = po.units[1];
             p.n_units = po.n_units[1]; p.n_zcopies = po.n_zcopies[1]; p.counter = h->counters + 1; p.stage_bytes = o.stage_bytes;
             size_t smem = mm_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_elems, 2, 0, ld);
-            (o.mm_variant & 2 ? hmatrix_mm_kernel<T, 2, true> : hmatrix_mm_kernel<T, 2, false>)<<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]), threads, smem, h->stream>>>(p);
+            const unsigned grid2 = (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]);
+            if (dfma) launch_mmf<T, 2>(mmf_ncol<T>(nc), grid2, threads, mmf_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_elems, 2, 0, ld), h->stream, p);
+            else
+            (o.mm_variant & 2 ? hmatrix_mm_kernel<T, 2, true> : hmatrix_mm_kernel<T, 2, false>)<<<grid2, threads, smem, h->stream>>>(p);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[3], h->stream));

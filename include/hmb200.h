@@ -72,7 +72,7 @@ typedef struct hmb200_options {
                                 stages that many operand ROWS of (mu + pad) per packet */
     int32_t mm_stage_bytes;  /* packet bytes of the multi-RHS phase-1 stream (default 40960) */
     int32_t mm_bin_cols;     /* entries of x per source bin, resident in shared memory in multi-RHS phase 1 (default 128) */
-    int32_t mm_variant;      /* tuning: 1 + bitmask (bit 0 / 1: double-buffered DMMA fragments in multi-RHS phase 1 / 2); 0 = default */
+    int32_t mm_variant;      /* tuning: 1 + bitmask (bit 0 / 1: double-buffered DMMA fragments in multi-RHS phase 1 / 2; bit 2: EXPERIMENTAL plain-DFMA consumer, csrc/kernels/mmf_kernels.cuh); 0 = default */
     int32_t reserved[1];
 } hmb200_options;
 

@@ -26,6 +26,8 @@ VARIANTS = [
     ("ctas = 2 x SMs", dict(ctas=2 * sms)),
     ("ctas = 2 x SMs, 40 KB packets", dict(ctas=2 * sms, stage_bytes=40960)),
     ("40 KB packets only", dict(stage_bytes=40960)),
+    ("EXPERIMENTAL DFMA consumer (mm_variant bit 2)", dict(mm_variant=1 + 4)),
+    ("EXPERIMENTAL DFMA consumer, ctas = 2 x SMs", dict(mm_variant=1 + 4, ctas=2 * sms)),
 ]
 
 

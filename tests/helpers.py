@@ -164,6 +164,23 @@ def bridge_available():
         return False
 
 
+def emulate_mmf(flat, op, alpha, X, beta, Y, **opts):
+    """the same product with the work split of the experimental DFMA consumer (kernels/mmf_kernels.cuh), lane by lane"""
+    emu = emulator()
+    o = _lib.hmb200_options()
+    for k, v in opts.items():
+        setattr(o, k, v)
+    cs = flat.c_struct()
+    a = (ctypes.c_double * 2)(complex(alpha).real, complex(alpha).imag)
+    b = (ctypes.c_double * 2)(complex(beta).real, complex(beta).imag)
+    X = np.ascontiguousarray(X, dtype=flat.np_dtype)
+    assert Y.flags.c_contiguous and Y.dtype == flat.np_dtype
+    rc = emu.plan_emulate_mmf(ctypes.byref(cs), flat.elem_bytes, ctypes.c_char(op.encode()), ctypes.byref(o), a,
+                              ctypes.c_void_p(X.ctypes.data), b, ctypes.c_void_p(Y.ctypes.data), int(X.shape[1]))
+    if rc:
+        raise RuntimeError(emu.plan_emulate_error().decode())
+
+
 def emulate_mm(flat, op, alpha, X, beta, Y, **opts):
     """Y = beta*Y + alpha*op(A)*X (row-major n x mu) through the multi-RHS packet streams, on the CPU."""
     emu = emulator()

@@ -437,6 +437,28 @@ def test_local_to_local_drivers_two_gpus():
         assert max(errs) < TOL, (rank, errs)
 
 
+@pytest.mark.skipif(not __import__("os").environ.get("HMB200_TEST_EXPERIMENTAL"), reason="experimental kernels: set HMB200_TEST_EXPERIMENTAL=1")
+@pytest.mark.parametrize("name,mu", [("d_N_cylinder", 8), ("d_N_cylinder", 64), ("d_N_rect", 37), ("d_SL_cylinder", 17), ("z_N_sphere", 5), ("z_HL_cylinder", 40)])
+def test_multi_rhs_dfma_experimental(name, mu):
+    """the plain-DFMA multi-RHS consumer (csrc/kernels/mmf_kernels.cuh, Options.mm_variant bit 2) vs the oracle; its index
+    arithmetic is checked on the CPU by tests/test_planner_emulated.py::test_dfma_consumer_mapping_*; not in the default suite
+    until it has run on a GPU"""
+    flat, _ = load_golden(name)
+    rng = np.random.default_rng(mu)
+    e = _engine(flat, build_transpose=1, mm_variant=1 + 4)
+    alpha, beta = (1.25, -0.75) if flat.dtype == "d" else (1.25 - 0.5j, 0.3 + 0.9j)
+    for op in _ops_of(flat):
+        n_in, n_out = (flat.n_cols, flat.n_rows) if op == "N" else (flat.n_rows, flat.n_cols)
+        X = np.ascontiguousarray(helpers.rand_vec(rng, n_in, flat.np_dtype, mu))
+        Y0 = np.ascontiguousarray(helpers.rand_vec(rng, n_out, flat.np_dtype, mu))
+        Y_ref = Y0.copy()
+        fo.add_matrix_product_row_major(flat, op, alpha, X, beta, Y_ref, mu)
+        Y = Y0.copy()
+        e.add_matrix_product_row_major(op, alpha, X, beta, Y, mu)
+        assert rel_err(Y, Y_ref) < TOL, (op, rel_err(Y, Y_ref))
+    e.close()
+
+
 @pytest.mark.parametrize("name,mu", [("d_N_cylinder", 64), ("d_N_rect", 70), ("d_SL_cylinder", 17), ("z_N_sphere", 32), ("z_HL_cylinder", 40), ("z_SL_sphere", 5)])
 def test_multi_rhs_dmma(name, mu):
     """Y = beta*Y + alpha*op(A)*X on the DMMA kernels (several passes, padded column tails) vs the oracle, and the
