@@ -64,6 +64,7 @@ EXPORTS = {
     "hmb200_kernel_ms_avg": (c_int, [c_void_p, POINTER(c_float * 4), POINTER(c_int)]),
     "hmb200_enable_timing": (c_int, [c_void_p, c_int]),
     "hmb200_launch_count": (c_int64, [c_void_p]),
+    "hmb200_fp64_rate": (c_int, [c_int, POINTER(c_double), POINTER(c_double)]),
     "hmb200_last_error": (c_char_p, []),
     "hmb200_version": (c_char_p, []),
 }

@@ -104,6 +104,9 @@ struct hmb200_handle {
         uint64_t products = 0; // collectives on the replicated buffers so far (fused products + gathers): selects the buffer
         uint64_t reduces = 0;  // all-reduces so far: selects the slot parity
         long long wait_cycles = 240000000000ll; // bound of the device-side waits (~2 minutes; HMB200_PEER_TIMEOUT_S overrides)
+        // error word of the bounded waits: page-locked MAPPED host memory, written by the kernels through err_dev and read by
+        // the host without any CUDA call, so every host-side synchronisation point can check it for free
+        int *err_host = nullptr, *err_dev = nullptr;
     } peer;
     void *pinned = nullptr;
     size_t pinned_bytes = 0;
@@ -301,7 +304,7 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
     CUDA_CHECK(cudaSetDevice(device));
     cudaDeviceProp prop;
     CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
-    if (prop.major < 9) throw std::runtime_error("device does not support bulk TMA copies (needs sm_100a)");
+    if (prop.major != 10) throw std::runtime_error("libhmb200.so holds sm_100a code only (B200); this device is sm_" + std::to_string(prop.major) + std::to_string(prop.minor));
     hmb200_handle *h = new hmb200_handle();
     try {
         h->device = device;
@@ -406,7 +409,7 @@ inline unsigned long long *peer_red_epoch(const hmb200_handle::Peer &pr, int par
 inline double *peer_red_slots(const hmb200_handle::Peer &pr, int q, int parity) {
     return reinterpret_cast<double *>(pr.region[q] + 2 * pr.buf_bytes + 512) + (size_t)parity * kMaxPeers * kPeerReduceMax;
 }
-inline int *peer_ctrl_err(const hmb200_handle::Peer &pr) { return reinterpret_cast<int *>(pr.region[pr.rank] + 2 * pr.buf_bytes + 192); }
+inline int *peer_ctrl_err(const hmb200_handle::Peer &pr) { return pr.err_dev; }
 
 // runs out = beta*out + alpha*op(A)*xz[0:n_in] on the handle's stream; x must already be in xz; y is a device pointer;
 // peer_buf >= 0: the phase-2 epilogue also stores the rows into buffer `peer_buf` of every rank and publishes the epoch
@@ -905,6 +908,7 @@ void hmb200_destroy(hmb200_handle *h) {
         if (!h->peer.region[q]) continue;
         if (q == h->peer.rank) cudaFree(h->peer.region[q]); else cudaIpcCloseMemHandle(h->peer.region[q]);
     }
+    if (h->peer.err_host) cudaFreeHost(h->peer.err_host);
     for (auto &po : h->ops) free_op(po);
     cudaFree(h->xz);
     cudaFree(h->ybuf);
@@ -968,6 +972,9 @@ int hmb200_peer_create(hmb200_handle *h, int n_ranks, int rank, int64_t n_global
         CUDA_CHECK(cudaMalloc(&r, pr.region_bytes));
         CUDA_CHECK(cudaMemset(r, 0, pr.region_bytes));
         pr.region[rank] = (uint8_t *)r;
+        CUDA_CHECK(cudaHostAlloc((void **)&pr.err_host, 64, cudaHostAllocMapped));
+        std::memset(pr.err_host, 0, 64);
+        CUDA_CHECK(cudaHostGetDevicePointer((void **)&pr.err_dev, pr.err_host, 0));
         cudaIpcMemHandle_t ih;
         CUDA_CHECK(cudaIpcGetMemHandle(&ih, r));
         static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
@@ -1002,8 +1009,7 @@ int hmb200_peer_buffer(hmb200_handle *h, int index, void **ptr) {
 int hmb200_peer_status(hmb200_handle *h, int *err) {
     return guarded([&] {
         if (!h || !err || !h->peer.region[h->peer.rank]) throw std::runtime_error("no peer region");
-        CUDA_CHECK(cudaSetDevice(h->device));
-        CUDA_CHECK(cudaMemcpy(err, peer_ctrl_err(h->peer), sizeof(int), cudaMemcpyDeviceToHost));
+        *err = *(volatile int *)h->peer.err_host; // covers the waits of all work that has completed on the stream
         return 0;
     });
 }

@@ -67,6 +67,12 @@ static void make_vleaves(const hmb200_flat &f, char op, Plan &plan) {
         v.r    = f.rank[l];
         v.kind = (uint8_t)HMB200_LEAF_DENSE_KIND(f.flags[l]);
         if (v.kind != 0 && v.r < 0) { // symv/hemv leaves are their own (conjugate) transpose: reference ignores trans (:21-24,:41-46)
+            // ... which is only right when op(leaf) == leaf: a symmetric ('S') leaf under 'C', or a Hermitian ('H') leaf under
+            // 'T', would need conj(leaf).  The root-level test above excludes them when the whole block carries the symmetry;
+            // a lone such leaf inside an 'N' block is refused like the root case rather than multiplied unconjugated.
+            const bool herm = v.kind >= 3;
+            if (plan.elem_bytes == 16 && ((op == 'C' && !herm) || (op == 'T' && herm)))
+                throw std::runtime_error(std::string("operation is not supported (trans=") + op + " on a dense leaf stored with symmetry " + (herm ? "H" : "S") + ")");
             transposed = false;
             conj       = false;
         }

@@ -79,7 +79,8 @@ __global__ void __launch_bounds__(256) peer_allreduce_kernel(const PeerReducePar
         const long long t0 = clock64();
         while (ptx::ld_acquire_sys_u64(p.my_flags + threadIdx.x) < target) {
             if (clock64() - t0 > p.max_cycles) {
-                atomicExch(p.err, 101 + (int)threadIdx.x);
+                *(volatile int *)p.err = 101 + (int)threadIdx.x; // mapped host memory (see peer_wait_kernel)
+                __threadfence_system();
                 break;
             }
             __nanosleep(100);

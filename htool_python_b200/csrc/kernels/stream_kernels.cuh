@@ -340,7 +340,8 @@ __global__ void peer_wait_kernel(const unsigned long long *flags, int n_ranks, c
     const long long t0 = clock64();
     while (ptx::ld_acquire_sys_u64(flags + q) < target) {
         if (clock64() - t0 > max_cycles) {
-            atomicExch(err, 1 + q);
+            *(volatile int *)err = 1 + q; // mapped host memory: a plain store (no PCIe atomics needed), made visible by the fence
+            __threadfence_system();
             break;
         }
         __nanosleep(200);

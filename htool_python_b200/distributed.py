@@ -81,16 +81,18 @@ def exchange_sum_slabs_(full, offs: List[int], sizes: List[int], out_local, beta
         return out_local
     rbuf = torch.empty((world, sizes[rank]), dtype=full.dtype, device=full.device)
     peer = lambda q: dist.get_global_rank(group, q) if group is not None else q  # noqa: E731
-    ops = []
+    ops, keep = [], []  # `keep`: the send buffers stay referenced until every request has completed
     for q in range(world):
         if q == rank:
             continue
         if sizes[q]:
-            ops.append(dist.P2POp(dist.isend, full[offs[q]:offs[q] + sizes[q]].contiguous(), peer(q), group))
+            keep.append(full[offs[q]:offs[q] + sizes[q]].contiguous())
+            ops.append(dist.P2POp(dist.isend, keep[-1], peer(q), group))
         if sizes[rank]:
             ops.append(dist.P2POp(dist.irecv, rbuf[q], peer(q), group))
     for req in (dist.batch_isend_irecv(ops) if ops else []):
         req.wait()
+    del keep
     for q in range(world):
         out_local.add_(mine if q == rank else rbuf[q])
     return out_local
@@ -154,6 +156,7 @@ class B200DistributedOperator:
         self._x = {}  # mu -> (x_cluster, y_cluster) replicated device buffers
         self._pin = {}
         self.fused = False
+        self._peer_failed = 0
         self.split_input_upload = True  # `matvec` on several GPUs: each rank uploads 1/P of x, NVLink exchange (needs identical x on all ranks)
         self._ybuf = None
         if fused_allgather is None:
@@ -198,6 +201,61 @@ class B200DistributedOperator:
             bufs.append(_device_tensor(ptr.value, self.n_target, self.is_complex, self.device))
         self._ybuf = {b.data_ptr(): b for b in bufs}
         self.fused = True
+        if self.world > 1 and self.n_source == self.n_target:
+            self._setup_shared_result()
+
+    def _setup_shared_result(self):
+        """One POSIX-shared, page-locked host buffer (two alternating result vectors + one flag line per rank) for the
+        replicated result of `matvec` on the ranks of one node: every rank downloads only ITS 1/P chunk of the user-numbered
+        result into it and a host-side flag tells the others, so a product moves n (not P*n) elements over PCIe.  The
+        reference's contract (src/htool/distributed_operator/distributed_operator.hpp:23-37: every rank returns the full
+        vector) is kept: the buffer is the same physical memory in every process."""
+        import warnings
+        from multiprocessing import resource_tracker, shared_memory
+
+        import torch
+        import torch.distributed as dist
+
+        self._shm = None
+        buf_bytes = (self.n_target * self.es + 4095) // 4096 * 4096
+        nbytes = 4096 + 2 * buf_bytes
+        name = [None]
+        if self.rank == 0:
+            try:
+                shm = shared_memory.SharedMemory(create=True, size=nbytes)
+                np.frombuffer(shm.buf, dtype=np.uint8, count=4096)[:] = 0
+                name[0] = shm.name
+            except Exception as e:  # no /dev/shm: keep the per-rank full download
+                warnings.warn(f"hmb200: shared result buffer unavailable ({e}); every rank downloads the full vector")
+        dist.broadcast_object_list(name, src=dist.get_global_rank(self.group, 0) if self.group is not None else 0, group=self.group)
+        ok = name[0] is not None
+        if ok and self.rank != 0:
+            try:
+                shm = shared_memory.SharedMemory(name=name[0])
+                try:  # the attaching processes must not unlink the segment at exit (3.12 registers them with the tracker)
+                    resource_tracker.unregister(shm._name, "shared_memory")
+                except Exception:
+                    pass
+            except Exception:
+                ok = False
+        if ok:
+            base = np.frombuffer(shm.buf, dtype=np.uint8)
+            with torch.cuda.device(self.device):
+                ok = int(torch.cuda.cudart().cudaHostRegister(base.ctypes.data, nbytes, 0)) == 0
+        oks = [None] * self.world
+        dist.all_gather_object(oks, bool(ok), group=self.group)
+        if not all(oks):
+            if ok:
+                torch.cuda.cudart().cudaHostUnregister(base.ctypes.data)
+            return
+        self._shm, self._shm_base, self._shm_calls = shm, base, 0
+        self._shm_flags = np.frombuffer(shm.buf, dtype=np.int64, count=512)[::8][:self.world]  # one 64-byte line per rank
+        self._shm_y = [np.frombuffer(shm.buf, dtype=self.np_dtype, count=self.n_target, offset=4096 + b * buf_bytes) for b in range(2)]
+        self._shm_y_t = [torch.from_numpy(a) for a in self._shm_y]
+        inv = torch.empty(self.n_target, dtype=torch.int32, device=self.device)
+        inv[self.perm_t.long()] = torch.arange(self.n_target, dtype=torch.int32, device=self.device)
+        self._inv_perm_t = inv  # y_user[i] = y_cluster[inv[i]]
+        self.shared_result_timeout_s = 120.0
 
     @property
     def shape(self):
@@ -221,6 +279,8 @@ class B200DistributedOperator:
 
         if not self.fused:
             raise RuntimeError("fused all-gather is not set up on this operator")
+        if self._peer_failed:
+            self.check_peers()
         eng = self.engine
         px, _ = eng._ptr(x_cluster, self.n_source, False)
         out = ctypes.c_void_p()
@@ -266,13 +326,33 @@ class B200DistributedOperator:
         _lib.check(_lib.lib().hmb200_peer_allreduce_f64(self.engine._h, t.data_ptr(), n))
         return t
 
-    def peer_status(self) -> int:
-        """0, or 1 + the rank whose epoch did not arrive within the wait kernel's bound (synchronises)"""
+    def peer_status(self, sync: bool = True) -> int:
+        """0, or 1 + the rank whose epoch did not arrive within a wait kernel's bound (101 + rank: an all-reduce).  The word
+        lives in mapped host memory; with sync=False it covers the waits that have already completed on the stream."""
         import ctypes
 
+        if not self.fused:
+            return 0
+        if sync:
+            import torch
+
+            torch.cuda.current_stream(self.device).synchronize()
         err = ctypes.c_int(0)
         _lib.check(_lib.lib().hmb200_peer_status(self.engine._h, ctypes.byref(err)))
         return err.value
+
+    def check_peers(self):
+        """to be called right after a host-side synchronisation: raises if a device-side wait of the peer collectives gave up
+        (a late or dead rank), instead of letting a partly gathered vector through.  The epochs are then out of step, so the
+        operator refuses further collectives."""
+        if not self.fused:
+            return
+        st = self.peer_status(sync=False)
+        if st or self._peer_failed:
+            self._peer_failed = self._peer_failed or st
+            what = f"all-reduce, rank {self._peer_failed - 101}" if self._peer_failed > 100 else f"rank {self._peer_failed - 1}"
+            raise RuntimeError(f"hmb200: a peer did not arrive within the wait bound ({what}; HMB200_PEER_TIMEOUT_S); "
+                               "the replicated vectors are incomplete and this operator must be rebuilt")
 
     def matvec_cluster_transposed_(self, x_cluster, y_cluster, trans: str = "T"):
         """y_cluster (replicated, length n_source) = op(A) x_cluster with op = transpose ('T') or conjugate transpose ('C'):
@@ -358,7 +438,10 @@ class B200DistributedOperator:
 
     def matvec(self, x, out=None):
         """`A * x` (user numbering, host arrays); `out`, when given, receives the result in place.  Page-locked numpy buffers
-        (`torch.Tensor.pin_memory().numpy()`) are DMA'd directly, pageable ones go through the operator's pinned staging."""
+        (`torch.Tensor.pin_memory().numpy()`) are DMA'd directly, pageable ones go through the operator's pinned staging.
+        `out="shared"` returns the operator's own result buffer without a copy: on several ranks of one node that is ONE
+        page-locked POSIX-shared vector every rank sees (each rank uploads 1/P of x and downloads 1/P of y), valid until the
+        call after the next."""
         import torch
 
         x = np.asarray(x)
@@ -366,8 +449,12 @@ class B200DistributedOperator:
             raise RuntimeError("Wrong dimension for HMatrix-vector product")  # distributed_operator.hpp:25-27
         if x.shape[0] != self.n_source:
             raise RuntimeError("Wrong size for HMatrix-vector product")
-        if out is not None and (not isinstance(out, np.ndarray) or out.dtype != self.np_dtype or out.shape != (self.n_target,) or not out.flags.c_contiguous):
-            raise ValueError("out must be a contiguous numpy array of the operator's dtype and target size")
+        if isinstance(out, str):
+            bad = out != "shared"
+        else:
+            bad = out is not None and (not isinstance(out, np.ndarray) or out.dtype != self.np_dtype or out.shape != (self.n_target,) or not out.flags.c_contiguous)
+        if bad:
+            raise ValueError("out must be a contiguous numpy array of the operator's dtype and target size, or the string 'shared'")
         (xu, xc, yc, yu), (pin_x, pin_y) = self._buffers(1)
         with torch.cuda.device(self.device):
             src = self._as_pinned_tensor(x)
@@ -387,14 +474,48 @@ class B200DistributedOperator:
                 xu.copy_(src, non_blocking=True)
             self._permute(True, self.perm_s, self.n_source, xu, xc, 1)     # global_to_root_cluster (:108)
             yc = self.matvec_cluster_fused_(xc) if self.fused else self.matvec_cluster_(xc, yc)
+            if self.fused and self.world > 1 and getattr(self, "_shm", None) is not None:
+                return self._finish_shared(yc, yu, out)
             self._permute(False, self.perm_t, self.n_target, yc, yu, 1)    # root_cluster_to_global (:117)
-            dst = self._as_pinned_tensor(out) if out is not None else None
+            dst = self._as_pinned_tensor(out) if isinstance(out, np.ndarray) else None
             (dst if dst is not None else pin_y).copy_(yu, non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
-        if out is None:
-            return pin_y.numpy().copy()
+        self.check_peers()
+        if out is None or isinstance(out, str):
+            return pin_y.numpy().copy() if out is None else pin_y.numpy()
         if dst is None:
             out[:] = pin_y.numpy()
+        return out
+
+    def _finish_shared(self, yc, yu, out):
+        """root_cluster_to_global of THIS rank's 1/P chunk of the user-numbered result, one D2H copy of that chunk into the
+        node-shared page-locked buffer, host-side flag, wait for the other ranks' flags.  Two result buffers alternate: a
+        rank can be at most one call ahead of the others, so a returned vector stays intact until the call after the next."""
+        import time
+
+        import torch
+
+        k = self._shm_calls
+        self._shm_calls += 1
+        b = k & 1
+        c0, c1 = self.rank * self.n_target // self.world, (self.rank + 1) * self.n_target // self.world
+        _lib.check(_lib.lib().hmb200_permute_gather(self._inv_perm_t.data_ptr() + 4 * c0, 0, c1 - c0, yc.data_ptr(), yu.data_ptr() + self.es * c0,
+                                                    self.es, 1, _lib.DEVICE, torch.cuda.current_stream(self.device).cuda_stream))
+        self._shm_y_t[b][c0:c1].copy_(yu[c0:c1], non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        self.check_peers()
+        fl = self._shm_flags
+        fl[self.rank] = k + 1
+        t0 = time.perf_counter()
+        while int(fl.min()) < k + 1:
+            if time.perf_counter() - t0 > self.shared_result_timeout_s:
+                raise RuntimeError(f"hmb200: rank {int(fl.argmin())} did not deliver its chunk of the result within {self.shared_result_timeout_s} s")
+        res = self._shm_y[b]
+        if isinstance(out, str):  # out="shared": the node-shared buffer itself (valid until the call after the next)
+            return res
+        if out is None:
+            return res.copy()
+        np.copyto(out, res)
         return out
 
     def _as_pinned_tensor(self, a):
@@ -436,5 +557,22 @@ class B200DistributedOperator:
         return np.array(pin_y.numpy().reshape((self.n_target, mu), order="F"), order="F")
 
     def close(self):
+        shm = getattr(self, "_shm", None)
+        if shm is not None:
+            import torch
+
+            try:
+                torch.cuda.current_stream(self.device).synchronize()
+                torch.cuda.cudart().cudaHostUnregister(self._shm_base.ctypes.data)
+            except Exception:
+                pass
+            self._shm_flags = self._shm_y = self._shm_y_t = self._shm_base = None
+            self._shm = None
+            try:
+                shm.close()
+                if self.rank == 0:
+                    shm.unlink()
+            except Exception:
+                pass
         if self._owns_engine:
             self.engine.close()

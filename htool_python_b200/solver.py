@@ -345,6 +345,12 @@ class CudaKrylovSpace:
         self.mm_min_cols = 5  # narrowest block that goes through the multi-RHS (DMMA) product, see matmat
         self.kernel_launches = 0
 
+    def _check_peers(self):
+        """after a host-side synchronisation: a wait of the peer collectives that gave up raises here (the Hessenberg
+        column just read would otherwise come from partly gathered / partly summed data)"""
+        if self.use_peer:
+            self.op.check_peers()
+
     # ---- storage ------------------------------------------------------------------------------------------------
     def vector(self):
         return self.torch.zeros(self.n_local, dtype=self.dtype, device=self.device)
@@ -411,6 +417,7 @@ class CudaKrylovSpace:
             self._permute(False, xg, self._xu)
             self._pin.copy_(self._xu, non_blocking=True)
             self.torch.cuda.current_stream(self.device).synchronize()
+        self._check_peers()
         return self._pin.numpy().copy()
 
     # ---- operator -----------------------------------------------------------------------------------------------
@@ -512,6 +519,7 @@ class CudaKrylovSpace:
         """one device->host read of a few scalars (the Hessenberg column): the only sync of an iteration"""
         flat = self.torch.cat([self.torch.view_as_real(h).reshape(-1) if h.is_complex() else h.reshape(-1).to(self.torch.float64) for h in handles])
         vals = flat.cpu().numpy()
+        self._check_peers()
         out, p = [], 0
         for h in handles:
             if h.is_complex():
@@ -536,6 +544,7 @@ class CudaKrylovSpace:
 
     def host_end(self, token):
         self._hev.synchronize()
+        self._check_peers()
         vals = self._hpin.numpy()
         out, p = [], 0
         for is_c, n in token:

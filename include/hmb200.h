@@ -139,7 +139,10 @@ int hmb200_add_sub_matrix_product_to_local_z(hmb200_handle *h, const double *in,
  *   2. exchange the 64-byte handles (any transport), then hmb200_peer_attach(h, handles: n_ranks x 64 bytes in rank order)
  *   3. collectively, the same number of times on every rank: hmb200_vector_product_allgather_{d,z}(h, alpha, in, &y):
  *      y (device pointer into this rank's region, n_global elements, cluster numbering) = alpha * A * in on all ranks;
- *      asynchronous on the handle's stream.  hmb200_peer_status reads the error word (non-zero: a peer did not arrive). */
+ *      asynchronous on the handle's stream.  hmb200_peer_status reads the error word (non-zero: 1 + the rank that did not
+ *      arrive within the bound of a product / gather wait, 101 + rank for an all-reduce).  The word lives in page-locked
+ *      mapped host memory, so the call costs nothing and covers every wait that has COMPLETED on the stream: call it after
+ *      any host-side synchronisation.  After an error the epochs are out of step: destroy the operator. */
 int hmb200_peer_create(hmb200_handle *h, int n_ranks, int rank, int64_t n_global, int slab_offset, unsigned char *ipc_handle_out);
 int hmb200_peer_attach(hmb200_handle *h, const unsigned char *ipc_handles);
 int hmb200_peer_buffer(hmb200_handle *h, int index, void **ptr);
@@ -201,6 +204,10 @@ int hmb200_kernel_ms_avg(hmb200_handle *h, float ms[4], int *n_products);
 int hmb200_enable_timing(hmb200_handle *h, int on);
 /* number of kernel launches issued by this handle since creation */
 int64_t hmb200_launch_count(const hmb200_handle *h);
+/* Diagnostics: measured FP64 issue rates of `device` in TFLOP/s -- tensor-core DMMA (mma.sync.m8n8k4.f64) and plain DFMA, 8
+ * warps per SM with 8 independent accumulators each; the roofline denominators of the multi-RHS path (no reference
+ * counterpart: bench.py reports them next to the achieved rate). */
+int hmb200_fp64_rate(int device, double *dmma_tflops, double *dfma_tflops);
 
 const char *hmb200_last_error(void);
 const char *hmb200_version(void);

@@ -21,7 +21,7 @@ torch.cuda.set_device(0)
 tree, H, flat, bt = bench.assemble(args, 1, 0, lambda m: print("[mm-sweep]", m, file=sys.stderr, flush=True))
 sms = torch.cuda.get_device_properties(0).multi_processor_count
 
-VARIANTS = [
+VARIANTS_ALL = [
     ("default (1 CTA / SM)", {}),
     ("ctas = 2 x SMs", dict(ctas=2 * sms)),
     ("ctas = 2 x SMs, 40 KB packets", dict(ctas=2 * sms, stage_bytes=40960)),
@@ -29,6 +29,9 @@ VARIANTS = [
     ("EXPERIMENTAL DFMA consumer (mm_variant bit 2)", dict(mm_variant=1 + 4)),
     ("EXPERIMENTAL DFMA consumer, ctas = 2 x SMs", dict(mm_variant=1 + 4, ctas=2 * sms)),
 ]
+
+sel = os.environ.get("MM_SWEEP_VARIANTS")
+VARIANTS = [VARIANTS_ALL[int(i)] for i in sel.split(",")] if sel else VARIANTS_ALL
 
 
 def timed(fn, reps=10, warm=2):
