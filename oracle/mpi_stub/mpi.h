@@ -89,12 +89,15 @@ MPISTUB_INLINE int MPI_Get_count(const MPI_Status *s, MPI_Datatype t, int *c) { 
 
 /* collectives on one rank */
 MPISTUB_INLINE int MPI_Allreduce(const void *s, void *r, int n, MPI_Datatype t, MPI_Op op, MPI_Comm c) { (void)op; (void)c; return mpistub_copy(s, r, n, t); }
+MPISTUB_INLINE int MPI_Reduce(const void *s, void *r, int n, MPI_Datatype t, MPI_Op op, int root, MPI_Comm c) { (void)op; (void)root; (void)c; return mpistub_copy(s, r, n, t); }
 MPISTUB_INLINE int MPI_Exscan(const void *s, void *r, int n, MPI_Datatype t, MPI_Op op, MPI_Comm c) { (void)s; (void)r; (void)n; (void)t; (void)op; (void)c; return MPI_SUCCESS; }
 MPISTUB_INLINE int MPI_Bcast(void *b, int n, MPI_Datatype t, int root, MPI_Comm c) { (void)b; (void)n; (void)t; (void)root; (void)c; return MPI_SUCCESS; }
 MPISTUB_INLINE int MPI_Gather(const void *s, int sn, MPI_Datatype st, void *r, int rn, MPI_Datatype rt, int root, MPI_Comm c) { (void)rn; (void)rt; (void)root; (void)c; return mpistub_copy(s, r, sn, st); }
 MPISTUB_INLINE int MPI_Gatherv(const void *s, int sn, MPI_Datatype st, void *r, const int *rn, const int *d, MPI_Datatype rt, int root, MPI_Comm c) { (void)rn; (void)root; (void)c; return mpistub_copy(s, (char *)r + (d ? (size_t)d[0] * rt : 0), sn, st); }
 MPISTUB_INLINE int MPI_Allgather(const void *s, int sn, MPI_Datatype st, void *r, int rn, MPI_Datatype rt, MPI_Comm c) { (void)rn; (void)rt; (void)c; return mpistub_copy(s, r, sn, st); }
 MPISTUB_INLINE int MPI_Allgatherv(const void *s, int sn, MPI_Datatype st, void *r, const int *rn, const int *d, MPI_Datatype rt, MPI_Comm c) { (void)rn; (void)c; return mpistub_copy(s, (char *)r + (d ? (size_t)d[0] * rt : 0), sn, st); }
+MPISTUB_INLINE int MPI_Alltoallv(const void *s, const int *sn, const int *sd, MPI_Datatype st, void *r, const int *rn, const int *rd, MPI_Datatype rt, MPI_Comm c) { (void)rn; (void)c; return mpistub_copy((const char *)s + (sd ? (size_t)sd[0] * st : 0), (char *)r + (rd ? (size_t)rd[0] * rt : 0), sn[0], st); }
+MPISTUB_INLINE int MPI_Barrier(MPI_Comm c) { (void)c; return MPI_SUCCESS; }
 MPISTUB_INLINE int MPI_Scatter(const void *s, int sn, MPI_Datatype st, void *r, int rn, MPI_Datatype rt, int root, MPI_Comm c) { (void)rn; (void)rt; (void)root; (void)c; return (r == MPI_IN_PLACE) ? MPI_SUCCESS : mpistub_copy(s, r, sn, st); }
 MPISTUB_INLINE int MPI_Scatterv(const void *s, const int *sn, const int *d, MPI_Datatype st, void *r, int rn, MPI_Datatype rt, int root, MPI_Comm c) { (void)sn; (void)root; (void)c; return (r == MPI_IN_PLACE) ? MPI_SUCCESS : mpistub_copy((const char *)s + (d ? (size_t)d[0] * st : 0), r, rn, rt); }
 MPISTUB_INLINE int MPI_Igather(const void *s, int sn, MPI_Datatype st, void *r, int rn, MPI_Datatype rt, int root, MPI_Comm c, MPI_Request *q) { *q = MPI_REQUEST_NULL; return MPI_Gather(s, sn, st, r, rn, rt, root, c); }
