@@ -401,7 +401,7 @@ def run_b200(args):
         passes = -(-mu // (64 if es == 8 else 32))
         flops = (2 if es == 8 else 8) * mu * flat.stored_coefficients
         tf = flops / (kms["total"] * passes * 1e-3) / 1e12 if kms["total"] > 0 else 0.0
-        roofline = {"bound": "tensor", "kernel": "hmatrix_mm_kernel<T,1|2> (mma.sync.m8n8k4.f64)", "achieved": round(tf, 2), "peak": dmma_tf,
+        roofline = {"bound": "tensor", "kernel": "hmatrix_mm_kernel<T,phase 1|2> panel GEMMs (mma.sync.m8n8k4.f64, SASS DMMA)", "achieved": round(tf, 2), "peak": dmma_tf,
                     "peak_source": "FP64 tensor-core (DMMA) issue rate measured in this run on this GPU (hmb200_fp64_rate; MEASURED_PEAKS.json has no FP64 figure)",
                     "unit": "TFLOP/s", "frac": round(tf / dmma_tf, 4) if dmma_tf else None, "traffic": None, "algorithmic_flops_per_step": flops, "passes": passes,
                     "kernel_ms_per_pass": {k: round(v, 4) for k, v in kms.items()}}

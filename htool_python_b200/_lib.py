@@ -13,7 +13,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libhmb200.so"
 
 class hmb200_options(ctypes.Structure):
     _fields_ = [(n, c_int32) for n in ("stage_bytes", "stage_z_bytes", "n_stages", "consumer_warps", "piece1_bytes", "piece2_bytes",
-                                       "bin_rows", "unit_stages", "ctas", "build_transpose", "no_matmat", "stage_z_elems", "mm_stage_bytes", "mm_bin_cols", "mm_variant")] + [("reserved", c_int32 * 1)]
+                                       "bin_rows", "unit_stages", "ctas", "build_transpose", "no_matmat", "mm_task_cols", "mm1_kg", "mm2_kg", "reserved0")] + [("reserved", c_int32 * 1)]
 
 
 class hmb200_info(ctypes.Structure):
@@ -43,6 +43,11 @@ EXPORTS = {
     "hmb200_peer_attach": (c_int, [c_void_p, c_void_p]),
     "hmb200_peer_buffer": (c_int, [c_void_p, c_int, POINTER(c_void_p)]),
     "hmb200_peer_status": (c_int, [c_void_p, POINTER(c_int)]),
+    "hmb200_peer_mm_create": (c_int, [c_void_p, c_int, c_void_p]),
+    "hmb200_peer_mm_attach": (c_int, [c_void_p, c_void_p]),
+    "hmb200_peer_mm_buffer": (c_int, [c_void_p, c_int, POINTER(c_void_p)]),
+    "hmb200_matrix_product_allgather_d": (c_int, [c_void_p, c_void_p, c_void_p, c_int, POINTER(c_void_p)]),
+    "hmb200_matrix_product_allgather_z": (c_int, [c_void_p, c_void_p, c_void_p, c_int, POINTER(c_void_p)]),
     "hmb200_peer_allgather": (c_int, [c_void_p, c_void_p, POINTER(c_void_p)]),
     "hmb200_peer_allgather_range": (c_int, [c_void_p, c_void_p, c_int64, c_int64, POINTER(c_void_p)]),
     "hmb200_peer_allreduce_f64": (c_int, [c_void_p, c_void_p, c_int]),
@@ -50,6 +55,8 @@ EXPORTS = {
     "hmb200_vector_product_allgather_z": (c_int, [c_void_p, c_void_p, c_void_p, POINTER(c_void_p)]),
     "hmb200_permute_gather": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "hmb200_permute_scatter": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "hmb200_block_to_rows": (c_int, [c_void_p, c_int, c_int, c_void_p, ctypes.c_longlong, c_void_p, c_int, c_void_p]),
+    "hmb200_rows_to_block": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, ctypes.c_longlong, c_int, c_void_p]),
     "hmb200_set_permutations": (c_int, [c_void_p, c_void_p, c_void_p]),
     "hmb200_matvec_user_d": (c_int, [c_void_p, c_void_p, c_void_p, c_int]),
     "hmb200_matvec_user_z": (c_int, [c_void_p, c_void_p, c_void_p, c_int]),

@@ -4,7 +4,6 @@
 #include "planner.h"
 #include "../kernels/stream_kernels.cuh"
 #include "../kernels/mm_kernels.cuh"
-#include "../kernels/mmf_kernels.cuh"
 #include "../kernels/peer_kernels.cuh"
 
 #include <chrono>
@@ -38,13 +37,13 @@ struct PackedOp {
     bool valid = false;
     char op    = 'N';
     int32_t n_in = 0, n_out = 0;
-    // index 0: phase 1, 1: phase 2, 2: multi-RHS phase 1 (source-bin grouped V tiles)
-    uint8_t *stream[3]    = {nullptr, nullptr, nullptr};
-    StageEntry *stages[3] = {nullptr, nullptr, nullptr};
-    ZCopy *zcopies[3]     = {nullptr, nullptr, nullptr};
-    WorkUnit *units[3]    = {nullptr, nullptr, nullptr};
-    uint32_t n_units[3]   = {0, 0, 0};
-    uint32_t n_zcopies[3] = {0, 0, 0};
+    // index 0: phase 1, 1: phase 2 (single RHS); 2, 3: the multi-RHS panel streams of phase 1 / phase 2 (plan.h "mm streams")
+    uint8_t *stream[4]    = {nullptr, nullptr, nullptr, nullptr};
+    StageEntry *stages[4] = {nullptr, nullptr, nullptr, nullptr};
+    ZCopy *zcopies[4]     = {nullptr, nullptr, nullptr, nullptr};
+    WorkUnit *units[4]    = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t n_units[4]   = {0, 0, 0, 0};
+    uint32_t n_zcopies[4] = {0, 0, 0, 0};
     ReduceSeg *reduce     = nullptr;
     uint32_t n_reduce     = 0;
     ReduceSeg *reduce_mm  = nullptr;
@@ -52,10 +51,12 @@ struct PackedOp {
     uint32_t n_reduce_mm  = 0;
     uint64_t xz_elems     = 0;
     uint64_t mm_rows      = 0;
+    uint32_t mm_zero_row  = 0;
+    uint32_t mm_packet_bytes[2] = {0, 0}; // largest packet of the two panel streams
     bool has_mm           = false;
     // bookkeeping
-    uint64_t stream_bytes[3] = {0, 0, 0};
-    uint64_t n_stages[3] = {0, 0, 0}, n_pieces[3] = {0, 0, 0};
+    uint64_t stream_bytes[4] = {0, 0, 0, 0};
+    uint64_t n_stages[4] = {0, 0, 0, 0}, n_pieces[4] = {0, 0, 0, 0};
     uint64_t table_bytes = 0;
     int n_bins = 0;
 };
@@ -68,6 +69,7 @@ struct hmb200_handle {
     int es              = 8;
     Options opt;
     int n_sms = 0;
+    size_t smem_optin = 0;
     int32_t n_rows = 0, n_cols = 0;
     PackedOp ops[3]; // N, T, C
     void *xz = nullptr;
@@ -101,6 +103,11 @@ struct hmb200_handle {
         size_t buf_bytes = 0, region_bytes = 0;
         uint8_t *region[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; // [rank] own allocation, others IPC-mapped
         bool attached = false;
+        // replicated row-major blocks (n_global x mm_mu) of the fused multi-RHS product: a second IPC region per rank, two blocks
+        uint8_t *mm_region[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+        size_t mm_buf_bytes = 0;
+        int mm_mu = 0;
+        bool mm_attached = false;
         uint64_t products = 0; // collectives on the replicated buffers so far (fused products + gathers): selects the buffer
         uint64_t reduces = 0;  // all-reduces so far: selects the slot parity
         long long wait_cycles = 240000000000ll; // bound of the device-side waits (~2 minutes; HMB200_PEER_TIMEOUT_S overrides)
@@ -180,7 +187,9 @@ void ensure_dev(void **p, uint64_t *have, uint64_t need_elems, int es) {
 
 // packs one phase's stream window by window through two pinned buffers and uploads it
 void upload_stream(hmb200_handle *h, const hmb200_flat &flat, const Plan &plan, int phase, uint8_t **dptr, double &pack_s, double &up_s) {
-    const PhasePlan &ph = phase == 1 ? plan.phase1 : (phase == 2 ? plan.phase2 : plan.phase1m);
+    struct View { const std::vector<StageEntry> &stages; uint64_t stream_bytes; };
+    const View ph = phase == 1 ? View{plan.phase1.stages, plan.phase1.stream_bytes} : phase == 2 ? View{plan.phase2.stages, plan.phase2.stream_bytes}
+                  : phase == 3 ? View{plan.mm1.stages, plan.mm1.stream_bytes} : View{plan.mm2.stages, plan.mm2.stream_bytes};
     CUDA_CHECK(cudaMalloc(dptr, (size_t)std::max<uint64_t>(ph.stream_bytes, 128)));
     if (ph.stages.empty()) return;
     const uint64_t window = std::min<uint64_t>(std::max<uint64_t>(ph.stream_bytes, 1 << 20), 256ull << 20);
@@ -226,8 +235,8 @@ void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) 
     po.n_out = plan.n_out;
     double pack_s = 0, up_s = 0;
     po.has_mm = h->opt.build_matmat != 0;
-    for (int ph = 0; ph < (po.has_mm ? 3 : 2); ph++) {
-        const PhasePlan &pp = ph == 0 ? plan.phase1 : (ph == 1 ? plan.phase2 : plan.phase1m);
+    for (int ph = 0; ph < 2; ph++) {
+        const PhasePlan &pp = ph == 0 ? plan.phase1 : plan.phase2;
         upload_stream(h, flat, plan, ph + 1, &po.stream[ph], pack_s, up_s);
         po.stages[ph]       = upload_vec(pp.stages, h->stream);
         po.zcopies[ph]      = upload_vec(pp.zcopies, h->stream);
@@ -238,13 +247,27 @@ void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) 
         po.n_stages[ph]     = pp.stages.size();
         po.table_bytes += pp.stages.size() * sizeof(StageEntry) + pp.zcopies.size() * sizeof(ZCopy) + pp.units.size() * sizeof(WorkUnit);
     }
+    for (int ph = 2; ph < (po.has_mm ? 4 : 2); ph++) {
+        const MmPhasePlan &pp = ph == 2 ? plan.mm1 : plan.mm2;
+        upload_stream(h, flat, plan, ph + 1, &po.stream[ph], pack_s, up_s);
+        po.stages[ph]       = upload_vec(pp.stages, h->stream);
+        po.zcopies[ph]      = upload_vec(pp.zcopies, h->stream);
+        po.units[ph]        = upload_vec(pp.units, h->stream);
+        po.n_units[ph]      = (uint32_t)pp.units.size();
+        po.n_zcopies[ph]    = (uint32_t)pp.zcopies.size();
+        po.stream_bytes[ph] = pp.stream_bytes;
+        po.n_stages[ph]     = pp.stages.size();
+        po.n_pieces[ph]     = pp.pieces.size();
+        po.mm_packet_bytes[ph - 2] = pp.max_packet_bytes;
+        po.table_bytes += pp.stages.size() * sizeof(StageEntry) + pp.zcopies.size() * sizeof(ZCopy) + pp.units.size() * sizeof(WorkUnit);
+    }
     po.n_pieces[0] = plan.pieces1.size();
     po.n_pieces[1] = plan.pieces2.size();
-    po.n_pieces[2] = plan.mm_tiles.size();
     po.reduce_mm   = upload_vec(plan.reduce_mm, h->stream);
     po.reduce_mm_rows = upload_vec(plan.reduce_mm_rows, h->stream);
     po.n_reduce_mm = (uint32_t)plan.reduce_mm.size();
     po.mm_rows     = plan.mm_rows;
+    po.mm_zero_row = plan.mm_zero_row;
     po.reduce      = upload_vec(plan.reduce, h->stream);
     po.n_reduce    = (uint32_t)plan.reduce.size();
     po.table_bytes += plan.reduce.size() * sizeof(ReduceSeg);
@@ -263,7 +286,7 @@ void build_op(hmb200_handle *h, const hmb200_flat &flat, char op, PackedOp &po) 
 void free_op(PackedOp &po) {
     cudaFree(po.reduce_mm);
     cudaFree(po.reduce_mm_rows);
-    for (int i = 0; i < 3; i++) {
+    for (int i = 0; i < 4; i++) {
         cudaFree(po.stream[i]);
         cudaFree(po.stages[i]);
         cudaFree(po.zcopies[i]);
@@ -286,13 +309,26 @@ inline int mm_ld(int nc, int es) {
     return nc8 + ((nc8 % 16 == 0) ? 4 : 12);
 }
 inline int mm_max_ld(int es) { return es == 16 ? 34 : 68; }
+inline int mm_pass_cols(int es) { return es == 8 ? 64 : 32; }
 
-template <typename T>
-bool mm_fits(const hmb200_handle *h, size_t smem_optin) {
+// shared memory of the multi-RHS kernels for a pass at row stride ld: ring depth that fits the opt-in limit (>= 2 or no launch)
+struct MmLaunchCfg { int stage_bytes, z_rows, n_stages; size_t smem; };
+inline MmLaunchCfg mm_launch_cfg(int phase, int es, uint32_t max_packet_bytes, int kg_per_packet, int ld, size_t smem_optin) {
+    MmLaunchCfg c{};
+    c.stage_bytes = (int)((std::max<uint32_t>(max_packet_bytes, 16) + 127) / 128 * 128);
+    c.z_rows      = kg_per_packet * (es == 8 ? 8 : 4);
+    int ns        = 6;
+    while (ns > 1 && mm_smem_bytes(phase, es, c.stage_bytes, c.z_rows, ns, ld) > smem_optin) ns--;
+    c.n_stages = ns;
+    c.smem     = mm_smem_bytes(phase, es, c.stage_bytes, c.z_rows, ns, ld);
+    return c;
+}
+inline bool mm_fits(const hmb200_handle *h, size_t smem_optin) {
     const Options &o = h->opt;
-    const int ld = mm_max_ld(h->es);
-    return mm_smem_bytes(1, h->es, o.mm_stage_bytes, 0, 2, o.mm_bin_cols, ld) <= smem_optin &&
-           mm_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_elems, 2, 0, ld) <= smem_optin;
+    const int ld = mm_max_ld(h->es), kgc = h->es == 8 ? 8 : 4;
+    const uint32_t p1 = 16 + (uint32_t)o.mm1_kg * (kMmRows1 / 8) * 512 + kMmRows1 * 4, p2 = 16 + (uint32_t)o.mm2_kg * (kMmRows2 / 8) * 512;
+    (void)kgc;
+    return mm_launch_cfg(1, h->es, p1, o.mm1_kg, ld, smem_optin).n_stages >= 2 && mm_launch_cfg(2, h->es, p2, o.mm2_kg, ld, smem_optin).n_stages >= 2;
 }
 
 hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, const hmb200_options *opt, int es) {
@@ -318,8 +354,9 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
         while (h->opt.n_stages > 2 && stream_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps) > (size_t)prop.sharedMemPerBlockOptin)
             h->opt.n_stages--;
         h->info = hmb200_info{};
-        if (h->opt.build_matmat && !(es == 8 ? mm_fits<double>(h, prop.sharedMemPerBlockOptin) : mm_fits<double2>(h, prop.sharedMemPerBlockOptin)))
-            h->opt.build_matmat = 0; // packet sizes chosen by the caller leave no room for the multi-RHS kernels' operand rows
+        h->smem_optin = (size_t)prop.sharedMemPerBlockOptin;
+        if (h->opt.build_matmat && !mm_fits(h, h->smem_optin))
+            h->opt.build_matmat = 0; // packet sizes chosen by the caller leave no room for two stages of the multi-RHS kernels
         build_op(h, *flat, 'N', h->ops[0]);
         if (h->opt.build_transpose) {
             const char sym = (char)flat->symmetry_for_leaves;
@@ -334,18 +371,6 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
         size_t s1 = stream_smem_bytes(1, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps);
         size_t s2 = stream_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_bytes, h->opt.n_stages, h->opt.consumer_warps);
         if (es == 8) set_kernel_attrs<double>(s1, s2); else set_kernel_attrs<double2>(s1, s2);
-        if (h->opt.build_matmat) {
-            const int ldm = mm_max_ld(es);
-            size_t m1 = mm_smem_bytes(1, es, h->opt.mm_stage_bytes, 0, 2, h->opt.mm_bin_cols, ldm), m2 = mm_smem_bytes(2, es, h->opt.stage_bytes, h->opt.stage_z_elems, 2, 0, ldm);
-            auto set2 = [&](auto k1a, auto k1b, auto k2a, auto k2b) {
-                CUDA_CHECK(cudaFuncSetAttribute(k1a, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m1));
-                CUDA_CHECK(cudaFuncSetAttribute(k1b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m1));
-                CUDA_CHECK(cudaFuncSetAttribute(k2a, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m2));
-                CUDA_CHECK(cudaFuncSetAttribute(k2b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)m2));
-            };
-            if (es == 8) set2(hmatrix_mm_kernel<double, 1, true>, hmatrix_mm_kernel<double, 1, false>, hmatrix_mm_kernel<double, 2, true>, hmatrix_mm_kernel<double, 2, false>);
-            else set2(hmatrix_mm_kernel<double2, 1, true>, hmatrix_mm_kernel<double2, 1, false>, hmatrix_mm_kernel<double2, 2, true>, hmatrix_mm_kernel<double2, 2, false>);
-        }
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
         // info
         const PackedOp &n = h->ops[0];
@@ -357,7 +382,7 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
         h->info.stream1_bytes = n.stream_bytes[0]; h->info.stream2_bytes = n.stream_bytes[1];
         h->info.table_bytes = n.table_bytes;
         h->info.workspace_bytes = (int64_t)h->xz_elems * es;
-        h->info.mm_stream_bytes = n.stream_bytes[2]; h->info.mm_tiles = n.n_pieces[2]; h->info.mm_stages = n.n_stages[2]; h->info.mm_rows = n.mm_rows;
+        h->info.mm_stream_bytes = n.stream_bytes[2] + n.stream_bytes[3]; h->info.mm_tiles = n.n_units[2]; h->info.mm_stages = n.n_stages[2] + n.n_stages[3]; h->info.mm_rows = n.mm_rows;
     } catch (...) {
         hmb200_destroy(h);
         throw;
@@ -581,42 +606,41 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
     return 0;
 }
 
-// ---- EXPERIMENTAL (Options.mm_variant bit 2): the DFMA consumer of mmf_kernels.cuh, one instantiation per pass width ----
-template <typename T>
-int mmf_ncol(int nc) {
-    const int nc8 = (nc + 7) & ~7;
-    if (nc8 <= 8) return 8;
-    if (nc8 <= 16 || sizeof(T) == 16) return 16;
-    return 32;
-}
+// ---- multi-RHS on the DMMA panel kernels (kernels/mm_kernels.cuh) --------------------------------------------------------------
 template <typename T, int PHASE>
-void launch_mmf(int ncol, unsigned grid, int threads, size_t smem, cudaStream_t st, const MmParams &p) {
+void launch_mm(bool wide, int nt, unsigned grid, size_t smem, cudaStream_t st, const MmParams &p) {
     auto go = [&](auto kern) {
         CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<grid, threads, smem, st>>>(p);
+        kern<<<grid, kMmThreads, smem, st>>>(p);
     };
-    if (ncol == 8) go(hmatrix_mmf_kernel<T, PHASE, 8>);
-    else if (ncol == 16) go(hmatrix_mmf_kernel<T, PHASE, 16>);
-    else if constexpr (sizeof(T) == 8) go(hmatrix_mmf_kernel<T, PHASE, 32>);
-    else throw std::runtime_error("mmf: complex passes hold at most 16 columns");
+    constexpr int MTW = PHASE == 1 ? 4 : 2, MTN = PHASE == 1 ? 2 : 1;   // m-tiles per warp: wide (4 x 2 warps) / narrow (8 x 1 warps)
+    constexpr int NTW = sizeof(T) == 8 ? 4 : 2;                         // n-tiles per warp of a wide pass (64 / 32 columns over 2 warp columns)
+    if (wide) go(hmatrix_mm_kernel<T, PHASE, 2, MTW, NTW>);
+    else if (nt <= 1) go(hmatrix_mm_kernel<T, PHASE, 1, MTN, 1>);
+    else if (nt <= 2) go(hmatrix_mm_kernel<T, PHASE, 1, MTN, 2>);
+    else if constexpr (sizeof(T) == 8) go(hmatrix_mm_kernel<T, PHASE, 1, MTN, 4>);
+    else throw std::runtime_error("internal: narrow complex passes hold at most 16 columns");
 }
 
-// ---- multi-RHS on the DMMA kernels ------------------------------------------------------------------------------
 // Y(:, c0:c0+nc) = beta*Y + alpha*op(A)*X(:, c0:c0+nc) for every pass of <= 64 (32 complex) columns.
 //   x: device; row-major n_in x mu (perm_in == nullptr), or COLUMN-major user block gathered through perm_in
 //   y: device, row-major n_out x mu (stride mu)
+//   peer_buf >= 0: the bin epilogue also stores the rows into block `peer_buf` of every rank (row stride mu) and the last pass
+//   publishes the epoch (fused all-gather of the row slabs)
 template <typename T>
-void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, const T *x, const int32_t *perm_in, T *y, int mu) {
+void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, const T *x, const int32_t *perm_in, T *y, int mu, int peer_buf = -1) {
     const Options &o = h->opt;
-    const bool dfma = (o.mm_variant & 4) != 0; // experimental DFMA consumer (mmf_kernels.cuh): passes of <= 32 (16 complex) columns
-    const int PC = dfma ? mmf_pass_cols<T>() : mm_pass_cols<T>();
-    const int threads = (kMmConsumerWarps + 1) * 32;
+    const int PC = mm_pass_cols(h->es);
     const int ctas = o.ctas > 0 ? o.ctas : h->n_sms;
+    ensure_dev(&h->ws_mm, &h->ws_mm_elems, (po.mm_rows + 4) * (uint64_t)mm_max_ld(h->es), h->es);
+    T *ws = (T *)h->ws_mm;
     for (int c0 = 0; c0 < mu; c0 += PC) {
-        const int nc = std::min(PC, mu - c0);
+        const int nc = std::min(PC, mu - c0), nc8 = (nc + 7) & ~7;
         const int ld = mm_ld(nc, h->es);
-        ensure_dev(&h->ws_mm, &h->ws_mm_elems, (po.mm_rows + 4) * (uint64_t)mm_max_ld(h->es), h->es);
-        T *ws = (T *)h->ws_mm;
+        const bool wide = nc8 > PC / 2;
+        const int nt = nc8 / 8;
+        // the zero rows (operand of K padding) at this pass's stride; x rows of the pass
+        CUDA_CHECK(cudaMemsetAsync(ws + (size_t)po.mm_zero_row * ld, 0, (size_t)kMmZeroRows * ld * sizeof(T), h->stream));
         {
             const size_t total = (size_t)po.n_in * nc;
             const unsigned g = (unsigned)std::min<size_t>((total + 255) / 256 + 1, 148 * 16);
@@ -639,32 +663,35 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
         p.ws = ws; p.ld = ld; p.ncols = nc; p.y = y + c0; p.ldy = mu;
         p.alpha_re = alpha[0]; p.alpha_im = h->es == 16 ? alpha[1] : 0.0;
         p.beta_re  = beta[0];  p.beta_im  = h->es == 16 ? beta[1] : 0.0;
-        p.n_stages = 2; p.z_rows = o.stage_z_elems; p.x_rows = o.mm_bin_cols;
         if (po.n_units[2] > 0) {
+            const MmLaunchCfg c = mm_launch_cfg(1, h->es, po.mm_packet_bytes[0], o.mm1_kg, ld, h->smem_optin);
             p.stream = po.stream[2]; p.stages = po.stages[2]; p.zcopies = po.zcopies[2]; p.units = po.units[2];
-            p.n_units = po.n_units[2]; p.n_zcopies = 0; p.counter = h->counters; p.stage_bytes = o.mm_stage_bytes;
-            size_t smem = mm_smem_bytes(1, h->es, o.mm_stage_bytes, 0, 2, o.mm_bin_cols, ld);
-            const unsigned grid1 = (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[2]);
-            if (dfma) launch_mmf<T, 1>(mmf_ncol<T>(nc), grid1, threads, mmf_smem_bytes(1, h->es, o.mm_stage_bytes, 0, 2, o.mm_bin_cols, ld), h->stream, p);
-            else
-            (o.mm_variant & 1 ? hmatrix_mm_kernel<T, 1, true> : hmatrix_mm_kernel<T, 1, false>)<<<grid1, threads, smem, h->stream>>>(p);
+            p.n_units = po.n_units[2]; p.counter = h->counters; p.stage_bytes = c.stage_bytes; p.z_rows = c.z_rows; p.n_stages = c.n_stages;
+            launch_mm<T, 1>(wide, nt, (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[2]), c.smem, h->stream, p);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[1], h->stream));
         if (po.n_reduce_mm > 0) {
             unsigned blocks = std::min<unsigned>((po.n_reduce_mm + 7) / 8, 148 * 32);
-            reduce_rows_kernel<T><<<blocks, 256, 0, h->stream>>>(po.reduce_mm, po.reduce_mm_rows, po.n_reduce_mm, ws, ld, (nc + 7) & ~7);
+            reduce_rows_kernel<T><<<blocks, 256, 0, h->stream>>>(po.reduce_mm, po.reduce_mm_rows, po.n_reduce_mm, ws, ld, nc8);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[2], h->stream));
-        if (po.n_units[1] > 0) {
-            p.stream = po.stream[1]; p.stages = po.stages[1]; p.zcopies = po.zcopies[1]; p.units = po.units[1];
-            p.n_units = po.n_units[1]; p.n_zcopies = po.n_zcopies[1]; p.counter = h->counters + 1; p.stage_bytes = o.stage_bytes;
-            size_t smem = mm_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_elems, 2, 0, ld);
-            const unsigned grid2 = (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]);
-            if (dfma) launch_mmf<T, 2>(mmf_ncol<T>(nc), grid2, threads, mmf_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_elems, 2, 0, ld), h->stream, p);
-            else
-            (o.mm_variant & 2 ? hmatrix_mm_kernel<T, 2, true> : hmatrix_mm_kernel<T, 2, false>)<<<grid2, threads, smem, h->stream>>>(p);
+        if (po.n_units[3] > 0) {
+            const MmLaunchCfg c = mm_launch_cfg(2, h->es, po.mm_packet_bytes[1], o.mm2_kg, ld, h->smem_optin);
+            p.stream = po.stream[3]; p.stages = po.stages[3]; p.zcopies = po.zcopies[3]; p.units = po.units[3];
+            p.n_units = po.n_units[3]; p.counter = h->counters + 1; p.stage_bytes = c.stage_bytes; p.z_rows = c.z_rows; p.n_stages = c.n_stages;
+            if (peer_buf >= 0) { // replicate the slab's rows into every rank's block; the epoch is published by the LAST pass only
+                const hmb200_handle::Peer &pr = h->peer;
+                const size_t slab_b = ((size_t)pr.slab_offset * mu + c0) * sizeof(T);
+                for (int q = 0; q < pr.n_ranks; q++) {
+                    if (q != pr.rank) p.peer_y[p.n_peers++] = pr.mm_region[q] + (size_t)peer_buf * pr.mm_buf_bytes + slab_b;
+                    if (c0 + PC >= mu) p.peer_flags[p.n_flags++] = peer_ctrl_flags(pr, q, peer_buf) + pr.rank;
+                }
+                p.epoch = peer_ctrl_epoch(pr, peer_buf);
+                p.done  = peer_ctrl_done(pr);
+            }
+            launch_mm<T, 2>(wide, nt, (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[3]), c.smem, h->stream, p);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[3], h->stream));
@@ -864,6 +891,29 @@ int peer_allgather(hmb200_handle *h, const void *local_slab, void **y_out, int64
     return 0;
 }
 
+// Y_replicated (n_global x mu, row-major) = alpha * A_slab * in on EVERY rank: the multi-RHS slab product whose bin epilogue stores
+// each tile's rows into the replicated block of all ranks, then the wait for the epochs of all ranks (the MPI_Allgatherv of
+// add_distributed_operator_matrix_product_row_major_global_to_global.hpp:75 inside the kernel)
+template <typename T>
+int fused_mm_product(hmb200_handle *h, const double *alpha, const void *in, int mu, void **y_out) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    hmb200_handle::Peer &pr = h->peer;
+    if (!pr.attached || !pr.mm_attached) throw std::runtime_error("hmb200_peer_attach / hmb200_peer_mm_attach have not been called");
+    if (mu != pr.mm_mu) throw std::runtime_error("the replicated blocks were created for another number of right-hand sides");
+    PackedOp &po = h->ops[0];
+    if (!po.has_mm) throw std::runtime_error("the multi-RHS streams were not packed (no_matmat)");
+    const int buf = (int)(pr.products & 1);
+    pr.products++;
+    T *yb = reinterpret_cast<T *>(pr.mm_region[pr.rank] + (size_t)buf * pr.mm_buf_bytes);
+    const double zero[2] = {0.0, 0.0};
+    run_mm_product<T>(h, po, alpha, zero, (const T *)in, nullptr, yb + (size_t)pr.slab_offset * mu, mu, buf);
+    peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), pr.wait_cycles);
+    h->launches++;
+    CUDA_CHECK(cudaGetLastError());
+    if (y_out) *y_out = yb;
+    return 0;
+}
+
 template <typename F>
 int guarded(F &&f) {
     try {
@@ -907,6 +957,10 @@ void hmb200_destroy(hmb200_handle *h) {
     for (int q = 0; q < h->peer.n_ranks; q++) {
         if (!h->peer.region[q]) continue;
         if (q == h->peer.rank) cudaFree(h->peer.region[q]); else cudaIpcCloseMemHandle(h->peer.region[q]);
+    }
+    for (int q = 0; q < h->peer.n_ranks; q++) {
+        if (!h->peer.mm_region[q]) continue;
+        if (q == h->peer.rank) cudaFree(h->peer.mm_region[q]); else cudaIpcCloseMemHandle(h->peer.mm_region[q]);
     }
     if (h->peer.err_host) cudaFreeHost(h->peer.err_host);
     for (auto &po : h->ops) free_op(po);
@@ -1000,6 +1054,62 @@ int hmb200_peer_attach(hmb200_handle *h, const unsigned char *ipc_handles) {
         pr.attached = true;
         return 0;
     });
+}
+int hmb200_peer_mm_create(hmb200_handle *h, int mu, unsigned char *ipc_handle_out) {
+    return guarded([&] {
+        if (!h || !ipc_handle_out) throw std::runtime_error("null argument");
+        hmb200_handle::Peer &pr = h->peer;
+        if (!pr.region[pr.rank]) throw std::runtime_error("hmb200_peer_create has not been called");
+        if (mu < 1) throw std::runtime_error("mu must be positive");
+        CUDA_CHECK(cudaSetDevice(h->device));
+        CUDA_CHECK(cudaStreamSynchronize(h->stream));
+        for (int q = 0; q < pr.n_ranks; q++) { // a previous set of blocks (another mu) is released first
+            if (!pr.mm_region[q]) continue;
+            if (q == pr.rank) CUDA_CHECK(cudaFree(pr.mm_region[q])); else CUDA_CHECK(cudaIpcCloseMemHandle(pr.mm_region[q]));
+            pr.mm_region[q] = nullptr;
+        }
+        pr.mm_attached  = false;
+        pr.mm_mu        = mu;
+        pr.mm_buf_bytes = (((size_t)pr.n_global * mu * h->es) + 255) & ~(size_t)255;
+        void *r = nullptr;
+        CUDA_CHECK(cudaMalloc(&r, 2 * pr.mm_buf_bytes));
+        CUDA_CHECK(cudaMemset(r, 0, 2 * pr.mm_buf_bytes));
+        pr.mm_region[pr.rank] = (uint8_t *)r;
+        cudaIpcMemHandle_t ih;
+        CUDA_CHECK(cudaIpcGetMemHandle(&ih, r));
+        std::memcpy(ipc_handle_out, &ih, 64);
+        return 0;
+    });
+}
+int hmb200_peer_mm_attach(hmb200_handle *h, const unsigned char *ipc_handles) {
+    return guarded([&] {
+        if (!h) throw std::runtime_error("null handle");
+        hmb200_handle::Peer &pr = h->peer;
+        if (!pr.mm_region[pr.rank]) throw std::runtime_error("hmb200_peer_mm_create has not been called");
+        if (pr.n_ranks > 1 && !ipc_handles) throw std::runtime_error("null argument");
+        CUDA_CHECK(cudaSetDevice(h->device));
+        for (int q = 0; q < pr.n_ranks; q++) {
+            if (q == pr.rank || pr.mm_region[q]) continue;
+            cudaIpcMemHandle_t ih;
+            std::memcpy(&ih, ipc_handles + 64 * (size_t)q, 64);
+            void *m = nullptr;
+            CUDA_CHECK(cudaIpcOpenMemHandle(&m, ih, cudaIpcMemLazyEnablePeerAccess));
+            pr.mm_region[q] = (uint8_t *)m;
+        }
+        pr.mm_attached = true;
+        return 0;
+    });
+}
+int hmb200_peer_mm_buffer(hmb200_handle *h, int index, void **ptr) {
+    if (!h || !ptr || index < 0 || index > 1 || !h->peer.mm_region[h->peer.rank]) { g_last_error = "no multi-RHS peer region / bad index"; return 1; }
+    *ptr = h->peer.mm_region[h->peer.rank] + (size_t)index * h->peer.mm_buf_bytes;
+    return 0;
+}
+int hmb200_matrix_product_allgather_d(hmb200_handle *h, const double *alpha, const double *in, int mu, void **y_replicated) {
+    return guarded([&] { if (!h || h->es != 8) throw std::runtime_error("handle is not a real (double) engine"); return fused_mm_product<double>(h, alpha, in, mu, y_replicated); });
+}
+int hmb200_matrix_product_allgather_z(hmb200_handle *h, const double *alpha, const double *in, int mu, void **y_replicated) {
+    return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return fused_mm_product<double2>(h, alpha, in, mu, y_replicated); });
 }
 int hmb200_peer_buffer(hmb200_handle *h, int index, void **ptr) {
     if (!h || !ptr || index < 0 || index > 1 || !h->peer.region[h->peer.rank]) { g_last_error = "no peer region / bad index"; return 1; }
@@ -1118,6 +1228,32 @@ int hmb200_permute_gather(const int32_t *perm, int off, int n, const void *in, v
 }
 int hmb200_permute_scatter(const int32_t *perm, int off, int n, const void *in, void *out, int elem_bytes, int mu, int mem, void *stream) {
     return permute_impl(false, perm, off, n, in, out, elem_bytes, mu, mem, stream);
+}
+
+// column-major (user) block <-> row-major block, optionally through a cluster permutation; device pointers
+static int block_layout(bool to_rows, const int32_t *perm, int n, int mu, const void *src, void *dst, long long col_stride, int elem_bytes, void *stream) {
+    return guarded([&] {
+        if (elem_bytes != 8 && elem_bytes != 16) throw std::runtime_error("elem_bytes must be 8 or 16");
+        if (n < 0 || mu < 0 || col_stride < n) throw std::runtime_error("bad block shape");
+        if (n == 0 || mu == 0) return 0;
+        cudaStream_t s = (cudaStream_t)stream;
+        const unsigned g = (unsigned)std::min<size_t>(((size_t)n * mu + 255) / 256 + 1, 148 * 16);
+        if (elem_bytes == 8) {
+            if (to_rows) mm_load_rows_kernel<double><<<g, 256, 0, s>>>((const double *)src, 0, n, mu, (double *)dst, mu, perm, col_stride);
+            else mm_store_user_kernel<double><<<g, 256, 0, s>>>((const double *)src, n, mu, (double *)dst, perm, col_stride);
+        } else {
+            if (to_rows) mm_load_rows_kernel<double2><<<g, 256, 0, s>>>((const double2 *)src, 0, n, mu, (double2 *)dst, mu, perm, col_stride);
+            else mm_store_user_kernel<double2><<<g, 256, 0, s>>>((const double2 *)src, n, mu, (double2 *)dst, perm, col_stride);
+        }
+        CUDA_CHECK(cudaGetLastError());
+        return 0;
+    });
+}
+int hmb200_block_to_rows(const int32_t *perm, int n, int mu, const void *src_colmajor, long long col_stride, void *dst_rowmajor, int elem_bytes, void *stream) {
+    return block_layout(true, perm, n, mu, src_colmajor, dst_rowmajor, col_stride, elem_bytes, stream);
+}
+int hmb200_rows_to_block(const int32_t *perm, int n, int mu, const void *src_rowmajor, void *dst_colmajor, long long col_stride, int elem_bytes, void *stream) {
+    return block_layout(false, perm, n, mu, src_rowmajor, dst_colmajor, col_stride, elem_bytes, stream);
 }
 
 int hmb200_set_permutations(hmb200_handle *h, const int32_t *target_perm_local, const int32_t *source_perm_local) {

@@ -63,4 +63,29 @@ struct ReduceSeg { // 16 B: t[final_off + l] = sum_q xz[first_partial + q*len + 
     uint32_t len;
 };
 
+// ---- multi-RHS ("mm") streams: every unit is one panel GEMM  C (rows x mu) = A (rows x K) B (K x mu) -------------------------
+//   phase 1: A = V rows of the low-rank leaves that share one source cluster, stacked (<= 128 rows), K = a chunk of that
+//            cluster's columns, B = the rows of X for those columns, C = T rows (or partial T rows when K is split)
+//   phase 2: A = [U_1 | U_2 | ... | D_1 | ...] of ONE target bin (<= 64 rows), concatenated along K, B = the T rows / X rows of
+//            those leaves in the same order, C = the bin's rows of Y
+// A is packed FRAGMENT-MAJOR for mma.sync.m8n8k4.f64: the panel is cut into m-tiles of 8 rows and k-groups of kMmKg columns
+// (8 real / 4 complex); chunk (kg, mt) is 32 lanes x 16 bytes, lane = 4*gid + tig holding A[8 mt + gid][kMmKg kg + tig] (and
+// ... + 4 + tig for real), so that one 128-bit shared load per lane yields the A fragments of the whole k-group, conflict-free.
+// Packet = [MmPacketHeader 16 B][chunks, kg-major then mt][phase 1, last packet of a unit: uint32 row map].  The operand rows of
+// a packet are gathered into the stage's z-area by bulk copies (ZCopy: src_elem = workspace ROW, bytes / dst_off in units of
+// elem_bytes per row), in the order of the packet's K columns.
+constexpr uint32_t kMmFlagFirst = 1u, kMmFlagLast = 2u, kMmFlagTerminate = 4u;
+constexpr int kMmRows1 = 128; // rows of a phase-1 panel (16 m-tiles)
+constexpr int kMmRows2 = 64;  // rows of a phase-2 panel = a target bin (8 m-tiles)
+constexpr int kMmZeroRows = 8; // zero rows at the end of the workspace: the operand of K padding
+
+struct MmPacketHeader { // 16 B
+    uint32_t n_kg;      // k-groups in this packet
+    uint32_t out0;      // phase 2: first output row of the bin
+    uint16_t rows;      // rows of the panel
+    uint16_t mt_panel;  // m-tiles of the panel = ceil(rows / 8)
+    uint16_t flags;     // kMmFlag*
+    uint16_t map_off16; // phase 1, last packet: offset of the row map in 16-byte units (one destination workspace row per panel row)
+};
+
 } // namespace hmb200

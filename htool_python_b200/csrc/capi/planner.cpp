@@ -30,10 +30,9 @@ Options resolve_options(const hmb200_options *o) {
         if (o->ctas > 0) r.ctas = o->ctas;
         r.build_transpose = o->build_transpose;
         r.build_matmat    = o->no_matmat ? 0 : 1;
-        if (o->stage_z_elems > 0) r.stage_z_elems = o->stage_z_elems;
-        if (o->mm_stage_bytes > 0) r.mm_stage_bytes = o->mm_stage_bytes;
-        if (o->mm_bin_cols > 0) r.mm_bin_cols = o->mm_bin_cols;
-        if (o->mm_variant > 0) r.mm_variant = o->mm_variant - 1;
+        if (o->mm_task_cols > 0) r.mm_task_cols = o->mm_task_cols;
+        if (o->mm1_kg > 0) r.mm1_kg = o->mm1_kg;
+        if (o->mm2_kg > 0) r.mm2_kg = o->mm2_kg;
     }
     r.stage_bytes   = (int)align_up((uint32_t)std::max(r.stage_bytes, 2048), 128);
     r.stage_z_bytes = (int)align_up((uint32_t)std::min(std::max(r.stage_z_bytes, 1024), 65536 - 128), 128);
@@ -44,9 +43,9 @@ Options resolve_options(const hmb200_options *o) {
     r.piece1_bytes  = std::min(std::max(r.piece1_bytes, 256), piece_cap);
     r.piece2_bytes  = std::min(std::max(r.piece2_bytes, 256), piece_cap);
     r.unit_stages   = std::max(r.unit_stages, 1);
-    r.stage_z_elems  = std::min(std::max(r.stage_z_elems, 8), 4096);
-    r.mm_stage_bytes = (int)align_up((uint32_t)std::max(r.mm_stage_bytes, 2048), 128);
-    r.mm_bin_cols    = std::min(std::max(r.mm_bin_cols, 4), 4096);
+    r.mm1_kg       = std::min(std::max(r.mm1_kg, 1), 6);   // 8 KiB per k-group of a 128-row panel
+    r.mm2_kg       = std::min(std::max(r.mm2_kg, 1), 12);  // 4 KiB per k-group of a 64-row panel
+    r.mm_task_cols = std::max(r.mm_task_cols, 8);
     return r;
 }
 
@@ -220,13 +219,6 @@ struct StageBuilder {
         data_bytes += align_up(tile, 16);
         n_pieces++;
     }
-    // piece whose operand is already resident in shared memory (multi-RHS phase 1): only its row offset is recorded
-    void add_resident(uint32_t tile, uint32_t z_row) {
-        ph.piece_zoff.push_back((uint16_t)z_row);
-        tile_bytes.push_back(align_up(tile, 16));
-        data_bytes += align_up(tile, 16);
-        n_pieces++;
-    }
     static uint32_t z_need(int es, uint32_t z_src, uint32_t z_cnt) {
         uint32_t a, b, c; aligned_span(es, z_src, z_cnt, a, b, c); return b;
     }
@@ -249,148 +241,219 @@ struct StageBuilder {
 };
 
 // ------------------------------------------------------------------------------------------------------------
-// multi-RHS phase 1: T_j (r x mu) = V_j (r x n) X[cols_j] (n x mu), V tiles grouped by source bin
-// (reference: the first gemm of hmatrix/lrmat/linalg/add_lrmat_matrix_product_row_major.hpp:11-27)
+// multi-RHS panel streams (plan.h "mm streams"; reference: the leaf loop of
+// hmatrix/linalg/add_hmatrix_matrix_product_row_major.hpp:57-178 with the two gemms of
+// lrmat/linalg/add_lrmat_matrix_product_row_major.hpp:11-27 and the dense gemm of
+// matrix/linalg/add_matrix_matrix_product_row_major.hpp:23-46)
 // ------------------------------------------------------------------------------------------------------------
-static void build_mm_phase1(const Options &opt, Plan &plan) {
-    const int es = plan.elem_bytes;
-    // source bins: <= mm_bin_cols input entries, cut at the leaves' source-cluster boundaries where possible
-    {
-        std::vector<int32_t> cuts{0, plan.n_in};
-        for (const VLeaf &v : plan.vleaves)
-            if (v.r > 0) { cuts.push_back(v.col_off); cuts.push_back(v.col_off + v.n); }
-        std::sort(cuts.begin(), cuts.end());
-        cuts.erase(std::unique(cuts.begin(), cuts.end()), cuts.end());
-        auto &bs = plan.src_bin_start;
-        bs.clear();
-        size_t i = 0;
-        while (i + 1 < cuts.size()) {
-            int s0 = cuts[i];
-            size_t j = i + 1;
-            while (j + 1 < cuts.size() && cuts[j + 1] - s0 <= opt.mm_bin_cols) j++;
-            int e0 = cuts[j];
-            if (e0 - s0 <= opt.mm_bin_cols) bs.push_back(s0);
-            else {
-                int parts = (e0 - s0 + opt.mm_bin_cols - 1) / opt.mm_bin_cols;
-                for (int q = 0; q < parts; q++) bs.push_back(s0 + (int)((int64_t)(e0 - s0) * q / parts));
+namespace {
+
+struct MmBuilder {
+    MmPhasePlan &ph;
+    int es, kg_cols, kg_per_packet, panel_rows_max;
+    uint32_t zero_row;
+    // current unit
+    uint32_t unit_first = 0;
+    // current packet
+    uint32_t first_piece = 0, z_first = 0, kfill = 0, z_rows = 0;
+    uint16_t rows = 0, flags = 0;
+    uint32_t out0 = 0;
+
+    MmBuilder(MmPhasePlan &p, int e, int kgc, int kgpp, int prm, uint32_t zr) : ph(p), es(e), kg_cols(kgc), kg_per_packet(kgpp), panel_rows_max(prm), zero_row(zr) {}
+    uint32_t packet_cols() const { return (uint32_t)kg_cols * kg_per_packet; }
+
+    void begin_unit(uint16_t panel_rows, uint32_t out_row0) {
+        unit_first = (uint32_t)ph.stages.size();
+        rows = panel_rows; out0 = out_row0;
+        flags = (uint16_t)kMmFlagFirst;
+        begin_packet();
+    }
+    void begin_packet() {
+        first_piece = (uint32_t)ph.pieces.size();
+        z_first = (uint32_t)ph.zcopies.size();
+        kfill = 0; z_rows = 0;
+    }
+    void add_rows(uint32_t src_row, uint32_t n) { // operand rows for the next n columns of the packet
+        if (ph.zcopies.size() > z_first) {
+            ZCopy &zc = ph.zcopies.back();
+            if (zc.src_elem + zc.bytes / (uint32_t)es == src_row && (uint32_t)zc.bytes + n * es <= 65520u) { // contiguous in the workspace: extend
+                zc.bytes = (uint16_t)(zc.bytes + n * es);
+                z_rows += n;
+                return;
             }
+        }
+        ZCopy zc; zc.src_elem = src_row; zc.bytes = (uint16_t)(n * es); zc.dst_off = (uint16_t)(z_rows * es);
+        ph.zcopies.push_back(zc);
+        z_rows += n;
+    }
+    // appends columns [c0, c0+nc) of a role matrix (rows [r0, r0+nr) at panel row ro), whose operand rows start at src_row
+    void add_columns(int32_t vleaf, int32_t r0, int32_t nr, int32_t c0, int32_t nc, int32_t ro, uint32_t src_row) {
+        while (nc > 0) {
+            if (kfill == packet_cols()) { close_packet(false, UINT32_MAX); begin_packet(); }
+            const int32_t take = std::min<int32_t>(nc, (int32_t)(packet_cols() - kfill));
+            ph.pieces.push_back(MmPiece{vleaf, r0, nr, c0, take, ro, (int32_t)kfill});
+            add_rows(src_row, (uint32_t)take);
+            kfill += take; c0 += take; nc -= take; src_row += take;
+        }
+    }
+    void close_packet(bool last, uint32_t map_first) {
+        const uint32_t n_kg = (kfill + kg_cols - 1) / kg_cols;
+        if (n_kg * kg_cols > kfill) add_rows(zero_row, n_kg * kg_cols - kfill); // K padding multiplies zero rows (never NaNs of a neighbour)
+        if (last) flags |= (uint16_t)kMmFlagLast;
+        const uint32_t mt = ((uint32_t)rows + 7) / 8;
+        uint32_t bytes = 16 + n_kg * mt * 512;
+        if (map_first != UINT32_MAX) bytes += align_up((uint32_t)rows * 4, 16);
+        StageEntry se{};
+        se.gmem_off = ph.stream_bytes; se.bytes = bytes; se.z_first = z_first; se.n_z = (uint32_t)ph.zcopies.size() - z_first; se.z_bytes = z_rows * es;
+        ph.stages.push_back(se);
+        ph.packets.push_back(MmPacketHost{first_piece, (uint32_t)ph.pieces.size() - first_piece, n_kg, out0, rows, flags, map_first});
+        ph.stream_bytes = align_up64(ph.stream_bytes + bytes, 128);
+        ph.max_packet_bytes = std::max(ph.max_packet_bytes, bytes);
+        ph.max_z_rows = std::max(ph.max_z_rows, z_rows);
+        flags = 0;
+    }
+    void end_unit(uint32_t map_first) {
+        close_packet(true, map_first);
+        ph.units.push_back(WorkUnit{unit_first, (uint32_t)ph.stages.size() - unit_first});
+    }
+};
+
+} // namespace
+
+static void build_mm_streams(const Options &opt, Plan &plan) {
+    const int es = plan.elem_bytes, kgc = es == 8 ? 8 : 4;
+    const size_t nv = plan.vleaves.size();
+    // ---- workspace rows: x | T (tight, view order) | partials | zero rows ------------------------------------------------
+    plan.mm_t_row.assign(nv, 0);
+    uint64_t row = (uint64_t)plan.n_in;
+    for (size_t vi = 0; vi < nv; vi++)
+        if (plan.vleaves[vi].r > 0) { plan.mm_t_row[vi] = (uint32_t)row; row += (uint64_t)plan.vleaves[vi].r; }
+    const uint64_t t_end = row;
+
+    // ---- phase 1: panels of V rows sharing one source cluster, split into column chunks ----------------------------------------
+    struct Entry { uint32_t vleaf; int32_t l0, lr, ro; };
+    struct Panel { int32_t col_off, n; uint32_t first_entry, n_entries; int32_t rows; };
+    std::vector<Entry> entries;
+    std::vector<Panel> panels;
+    {
+        std::vector<uint32_t> order;
+        for (size_t vi = 0; vi < nv; vi++)
+            if (plan.vleaves[vi].r > 0) order.push_back((uint32_t)vi);
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+            const VLeaf &x = plan.vleaves[a], &y = plan.vleaves[b];
+            if (x.col_off != y.col_off) return x.col_off < y.col_off;
+            return x.n > y.n;
+        });
+        for (size_t i = 0; i < order.size();) {
+            const VLeaf &v0 = plan.vleaves[order[i]];
+            size_t j = i;
+            Panel cur{v0.col_off, v0.n, (uint32_t)entries.size(), 0, 0};
+            for (; j < order.size() && plan.vleaves[order[j]].col_off == v0.col_off && plan.vleaves[order[j]].n == v0.n; j++) {
+                const VLeaf &v = plan.vleaves[order[j]];
+                int l0 = 0;
+                while (l0 < v.r) { // a view may straddle two panels: panels are filled to kMmRows1 rows
+                    if (cur.rows == kMmRows1) {
+                        panels.push_back(cur);
+                        cur = Panel{v0.col_off, v0.n, (uint32_t)entries.size(), 0, 0};
+                    }
+                    const int take = std::min(v.r - l0, kMmRows1 - cur.rows);
+                    entries.push_back(Entry{order[j], l0, take, cur.rows});
+                    cur.n_entries++; cur.rows += take; l0 += take;
+                }
+            }
+            if (cur.rows > 0) panels.push_back(cur);
             i = j;
         }
-        bs.push_back(plan.n_in);
-        if (plan.n_in == 0) bs.assign(1, 0);
     }
-    const auto &bs   = plan.src_bin_start;
-    const int n_sbin = (int)bs.size() - 1;
-    auto sbin_of = [&](int col) { return (int)(std::upper_bound(bs.begin(), bs.end(), col) - bs.begin()) - 1; };
-    const uint32_t piece_cap = (uint32_t)(opt.mm_stage_bytes - 16 - 16 - 64);
-    // rows a tile of nq columns may have: a multiple of 16 (one DMMA row pair per warp item) that fits a packet
-    auto rows_cap = [&](int nq) { return std::min(128, std::max(8, (int)(piece_cap / ((uint32_t)nq * es)) / 16 * 16)); };
-
-    // ---- sub-pieces: (leaf rows l0..l0+lr) x (columns of one source bin, possibly sub-chunked) -----------------------
-    struct Sub { int b; int k_abs; Piece1 p; uint32_t seg; };
-    std::vector<Sub> subs;
-    for (size_t vi = 0; vi < plan.vleaves.size(); vi++) {
-        const VLeaf &v = plan.vleaves[vi];
-        if (v.r <= 0) continue;
-        const int b0 = sbin_of(v.col_off), b1 = sbin_of(v.col_off + v.n - 1);
-        struct Part { int b, k0, nq; };
-        std::vector<Part> parts;
-        for (int b = b0; b <= b1; b++) {
-            int cs = std::max(v.col_off, bs[b]), ce = std::min(v.col_off + v.n, bs[b + 1]);
-            if (ce <= cs) continue;
-            int nq_max = std::max(4, (int)(piece_cap / (8u * es)));
-            int nsub   = (ce - cs + nq_max - 1) / nq_max;
-            for (int q = 0; q < nsub; q++) {
-                int k0 = cs + (int)((int64_t)(ce - cs) * q / nsub), k1 = cs + (int)((int64_t)(ce - cs) * (q + 1) / nsub);
-                parts.push_back(Part{b, k0 - v.col_off, k1 - k0});
+    struct Task { uint32_t panel; int32_t k0, nk; int32_t chunk, n_chunks; uint32_t out_row; };
+    std::vector<Task> tasks;
+    std::vector<std::vector<uint32_t>> panel_part_rows(panels.size());
+    for (size_t pi = 0; pi < panels.size(); pi++) {
+        const Panel &pn = panels[pi];
+        const int nch = (pn.n + opt.mm_task_cols - 1) / opt.mm_task_cols;
+        for (int c = 0; c < nch; c++) {
+            const int k0 = (int)((int64_t)pn.n * c / nch), k1 = (int)((int64_t)pn.n * (c + 1) / nch);
+            uint32_t out_row = 0;
+            if (nch > 1) { out_row = (uint32_t)row; panel_part_rows[pi].push_back(out_row); row += (uint64_t)pn.rows; }
+            tasks.push_back(Task{(uint32_t)pi, k0, k1 - k0, c, nch, out_row});
+        }
+        if (nch > 1)
+            for (uint32_t e = pn.first_entry; e < pn.first_entry + pn.n_entries; e++) {
+                const Entry &en = entries[e];
+                ReduceSeg rs{plan.mm_t_row[en.vleaf] + (uint32_t)en.l0, (uint32_t)plan.reduce_mm_rows.size(), (uint32_t)nch, (uint32_t)en.lr};
+                for (uint32_t base : panel_part_rows[pi]) plan.reduce_mm_rows.push_back(base + (uint32_t)en.ro);
+                plan.reduce_mm.push_back(rs);
             }
-        }
-        int nq_big = 0;
-        for (const Part &pt : parts) nq_big = std::max(nq_big, pt.nq);
-        const int lmax = rows_cap(nq_big);
-        const int nl   = (v.r + lmax - 1) / lmax;
-        for (int li = 0; li < nl; li++) {
-            int l0 = (int)((int64_t)v.r * li / nl), l1 = (int)((int64_t)v.r * (li + 1) / nl), lr = l1 - l0;
-            const uint32_t seg = (uint32_t)plan.reduce_mm.size();
-            plan.reduce_mm.push_back(ReduceSeg{v.t_off + (uint32_t)l0, 0, 0, (uint32_t)lr});
-            for (const Part &pt : parts) subs.push_back(Sub{pt.b, v.col_off + pt.k0, Piece1{(int32_t)vi, l0, lr, pt.k0, pt.nq, 0}, seg});
-        }
     }
-    // same (bin, column range) => neighbours: they are stacked into one tile
-    std::stable_sort(subs.begin(), subs.end(), [](const Sub &x, const Sub &y) {
-        if (x.b != y.b) return x.b < y.b;
-        if (x.k_abs != y.k_abs) return x.k_abs < y.k_abs;
-        return x.p.nq > y.p.nq;
+    plan.mm_zero_row = (uint32_t)row;
+    row += kMmZeroRows;
+    if (row >= (1ull << 32)) throw std::runtime_error("multi-RHS workspace exceeds 2^32 rows; split the operator into slabs");
+    plan.mm_rows = row;
+    (void)t_end;
+    // units are visited by the first source column they read: concurrently running CTAs then share the rows of X in L2
+    std::stable_sort(tasks.begin(), tasks.end(), [&](const Task &a, const Task &b) {
+        return panels[a.panel].col_off + a.k0 < panels[b.panel].col_off + b.k0;
     });
-    // ---- tiles: stacks of sub-pieces sharing their columns; every tile writes a contiguous block of workspace rows ---
-    uint64_t rows = plan.xz_elems;
-    plan.pieces1m.resize(subs.size());
-    std::vector<int> tile_bin;
-    std::vector<std::vector<uint32_t>> seg_rows(plan.reduce_mm.size());
-    for (size_t i = 0; i < subs.size();) {
-        MmTile t{};
-        t.first_sub = (uint32_t)i;
-        t.nq        = (uint16_t)subs[i].p.nq;
-        t.zrow      = (uint16_t)(subs[i].k_abs - bs[subs[i].b]);
-        t.out_row   = (uint32_t)rows;
-        const int cap = rows_cap(subs[i].p.nq);
-        int r = 0;
-        size_t j = i;
-        while (j < subs.size() && subs[j].b == subs[i].b && subs[j].k_abs == subs[i].k_abs && subs[j].p.nq == subs[i].p.nq && (r == 0 || r + subs[j].p.lr <= cap)) {
-            Piece1 p  = subs[j].p;
-            p.out_off = (uint32_t)(rows + r);
-            plan.pieces1m[j] = p;
-            seg_rows[subs[j].seg].push_back(p.out_off);
-            r += p.lr;
-            j++;
-        }
-        t.n_sub = (uint32_t)(j - i);
-        t.rows  = (uint16_t)r;
-        rows += (uint64_t)r;
-        plan.mm_tiles.push_back(t);
-        tile_bin.push_back(subs[i].b);
-        i = j;
-    }
-    if (rows >= (1ull << 32)) throw std::runtime_error("multi-RHS workspace exceeds 2^32 rows; split the operator into slabs");
-    plan.mm_rows = rows;
-    for (size_t sg = 0; sg < plan.reduce_mm.size(); sg++) {
-        plan.reduce_mm[sg].first_partial = (uint32_t)plan.reduce_mm_rows.size();
-        plan.reduce_mm[sg].n_parts       = (uint32_t)seg_rows[sg].size();
-        plan.reduce_mm_rows.insert(plan.reduce_mm_rows.end(), seg_rows[sg].begin(), seg_rows[sg].end());
-    }
-    // ---- stages: one work unit per source bin; StageEntry.pad = (first x row, rows) of the bin's resident X slice ----
-    PhasePlan &ph = plan.phase1m;
-    StageBuilder sb(ph, opt, es);
-    sb.stage_cap = (uint32_t)opt.mm_stage_bytes;
-    sb.z_cap     = 0xffffffffu;
-    size_t ti = 0;
-    for (int b = 0; b < n_sbin; b++) {
-        size_t te = ti;
-        while (te < plan.mm_tiles.size() && tile_bin[te] == b) te++;
-        if (te == ti) continue; // no tile reads this slice of x
-        const uint32_t unit_first = (uint32_t)ph.stages.size();
-        sb.piece_base = 0;
-        sb.row0       = (uint32_t)bs[b];
-        sb.bin_rows   = (uint16_t)(bs[b + 1] - bs[b]);
-        sb.flags      = kFlagFirstOfBin;
-        sb.begin((uint32_t)ti);
-        for (; ti < te; ti++) {
-            const MmTile &t = plan.mm_tiles[ti];
-            uint32_t tile   = (uint32_t)t.rows * t.nq * es;
-            if (sb.n_pieces && !sb.fits(tile, 0)) {
-                sb.close();
-                sb.flags = 0;
-                sb.begin((uint32_t)ti);
+    {
+        MmBuilder mb(plan.mm1, es, kgc, opt.mm1_kg, kMmRows1, plan.mm_zero_row);
+        for (const Task &t : tasks) {
+            const Panel &pn = panels[t.panel];
+            mb.begin_unit((uint16_t)pn.rows, 0);
+            // the packet columns of a unit are the unit's source columns in order; every panel entry contributes its rows
+            for (int k = 0; k < t.nk;) {
+                if (mb.kfill == mb.packet_cols()) { mb.close_packet(false, UINT32_MAX); mb.begin_packet(); }
+                const int take = std::min<int>(t.nk - k, (int)(mb.packet_cols() - mb.kfill));
+                for (uint32_t e = pn.first_entry; e < pn.first_entry + pn.n_entries; e++) {
+                    const Entry &en = entries[e];
+                    plan.mm1.pieces.push_back(MmPiece{(int32_t)en.vleaf, en.l0, en.lr, t.k0 + k, take, en.ro, (int32_t)mb.kfill});
+                }
+                mb.add_rows((uint32_t)(pn.col_off + t.k0 + k), (uint32_t)take);
+                mb.kfill += take;
+                k += take;
             }
-            sb.add_resident(tile, t.zrow);
+            const uint32_t map_first = (uint32_t)plan.mm_row_map.size();
+            for (uint32_t e = pn.first_entry; e < pn.first_entry + pn.n_entries; e++) {
+                const Entry &en = entries[e];
+                for (int l = 0; l < en.lr; l++)
+                    plan.mm_row_map.push_back(t.n_chunks > 1 ? t.out_row + (uint32_t)(en.ro + l) : plan.mm_t_row[en.vleaf] + (uint32_t)(en.l0 + l));
+            }
+            mb.end_unit(map_first);
         }
-        sb.flags |= kFlagLastOfBin;
-        sb.close();
-        for (uint32_t s2 = unit_first; s2 < ph.stages.size(); s2++) {
-            ph.stages[s2].pad[0] = (uint32_t)bs[b];
-            ph.stages[s2].pad[1] = (uint32_t)(bs[b + 1] - bs[b]);
+    }
+    // ---- phase 2: one unit per target bin, its views concatenated along K --------------------------------------------------
+    {
+        MmBuilder mb(plan.mm2, es, kgc, opt.mm2_kg, kMmRows2, plan.mm_zero_row);
+        const int n_bins = (int)plan.bin_start.size() - 1;
+        auto bin_of = [&](int r) { return (int)(std::upper_bound(plan.bin_start.begin(), plan.bin_start.end(), r) - plan.bin_start.begin()) - 1; };
+        // views per bin, in view order (views are sorted by target range, so the T rows of a bin's views form few runs)
+        std::vector<uint64_t> first(n_bins + 1, 0);
+        for (size_t vi = 0; vi < nv; vi++) {
+            const VLeaf &v = plan.vleaves[vi];
+            for (int b = bin_of(v.row_off); b <= bin_of(v.row_off + v.m - 1); b++) first[b + 1]++;
         }
-        ph.units.push_back(WorkUnit{unit_first, (uint32_t)ph.stages.size() - unit_first});
+        for (int b = 0; b < n_bins; b++) first[b + 1] += first[b];
+        std::vector<uint32_t> bin_views(first[n_bins]);
+        {
+            std::vector<uint64_t> fill(first.begin(), first.end() - 1);
+            for (size_t vi = 0; vi < nv; vi++) {
+                const VLeaf &v = plan.vleaves[vi];
+                for (int b = bin_of(v.row_off); b <= bin_of(v.row_off + v.m - 1); b++) bin_views[fill[b]++] = (uint32_t)vi;
+            }
+        }
+        for (int b = 0; b < n_bins; b++) {
+            const int bs = plan.bin_start[b], be = plan.bin_start[b + 1];
+            mb.begin_unit((uint16_t)(be - bs), (uint32_t)bs);
+            for (uint64_t q = first[b]; q < first[b + 1]; q++) {
+                const uint32_t vi = bin_views[q];
+                const VLeaf &v = plan.vleaves[vi];
+                const int rs = std::max(v.row_off, bs), re = std::min(v.row_off + v.m, be);
+                if (re <= rs) continue;
+                const int K = v.r < 0 ? v.n : v.r;
+                const uint32_t src = v.r < 0 ? (uint32_t)v.col_off : plan.mm_t_row[vi];
+                mb.add_columns((int32_t)vi, rs - v.row_off, re - rs, 0, K, rs - bs, src);
+            }
+            mb.end_unit(UINT32_MAX); // a bin without views still gets one (empty) packet: beta must be applied
+        }
     }
 }
 
@@ -475,7 +538,6 @@ void build_plan(const hmb200_flat &f, int es, char op, const Options &opt, Plan 
                 if (nr <= 0) continue;
                 uint32_t nc_max = std::max<uint32_t>(1, (uint32_t)opt.piece2_bytes / (uint32_t)(nr * es));
                 nc_max          = std::min<uint32_t>(nc_max, std::min<uint32_t>(zmax_elems, 65535u));
-                nc_max          = std::min<uint32_t>(nc_max, (uint32_t)opt.stage_z_elems - 2);
                 int nch         = (int)((K + nc_max - 1) / nc_max);
                 for (int c = 0; c < nch; c++) {
                     int c0 = (int)((int64_t)K * c / nch), c1 = (int)((int64_t)K * (c + 1) / nch);
@@ -525,7 +587,6 @@ void build_plan(const hmb200_flat &f, int es, char op, const Options &opt, Plan 
     {
         PhasePlan &ph = plan.phase2;
         StageBuilder sb(ph, opt, es);
-        sb.z_cap = std::min<uint32_t>(sb.z_cap, (uint32_t)opt.stage_z_elems * es); // the multi-RHS kernel stages operand ROWS
         for (int b = 0; b < n_bins; b++) {
             uint32_t unit_first = (uint32_t)ph.stages.size();
             sb.piece_base       = 0;
@@ -548,8 +609,7 @@ void build_plan(const hmb200_flat &f, int es, char op, const Options &opt, Plan 
             ph.units.push_back(WorkUnit{unit_first, (uint32_t)ph.stages.size() - unit_first});
         }
     }
-    plan.mm_rows = plan.xz_elems;
-    if (opt.build_matmat) build_mm_phase1(opt, plan);
+    if (opt.build_matmat) build_mm_streams(opt, plan);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -572,33 +632,34 @@ static inline T sym_elem(const T *D, int n, int kind, int i, int j) {
 }
 
 template <typename T>
-static void fill_tile2(const hmb200_flat &f, const VLeaf &v, const Piece2 &p, T *dst) {
+static void fill_tile2(const hmb200_flat &f, const VLeaf &v, const Piece2 &p, T *dst, int ld = 0) {
     const int64_t l = v.leaf;
     const int lm = f.nrows[l];
+    if (ld <= 0) ld = p.nr;
     if (v.r < 0) {
         const T *D = (const T *)f.a[l];
         if (v.kind != 0) {
             for (int j = 0; j < p.nc; j++)
                 for (int i = 0; i < p.nr; i++)
-                    dst[(size_t)j * p.nr + i] = sym_elem(D, lm, v.kind, p.r0 + i, p.c0 + j);
+                    dst[(size_t)j * ld + i] = sym_elem(D, lm, v.kind, p.r0 + i, p.c0 + j);
         } else if (!v.transposed) {
             for (int j = 0; j < p.nc; j++)
-                std::memcpy(dst + (size_t)j * p.nr, D + (size_t)(p.c0 + j) * lm + p.r0, sizeof(T) * p.nr);
+                std::memcpy(dst + (size_t)j * ld, D + (size_t)(p.c0 + j) * lm + p.r0, sizeof(T) * p.nr);
         } else { // view = D^T (or D^H): view(i, j) = D(j, i)
             for (int j = 0; j < p.nc; j++)
                 for (int i = 0; i < p.nr; i++)
-                    dst[(size_t)j * p.nr + i] = conj_if(D[(size_t)(p.r0 + i) * lm + (p.c0 + j)], v.conj);
+                    dst[(size_t)j * ld + i] = conj_if(D[(size_t)(p.r0 + i) * lm + (p.c0 + j)], v.conj);
         }
     } else if (!v.transposed) { // U: lm x r
         const T *U = (const T *)f.a[l];
         for (int j = 0; j < p.nc; j++)
-            std::memcpy(dst + (size_t)j * p.nr, U + (size_t)(p.c0 + j) * lm + p.r0, sizeof(T) * p.nr);
+            std::memcpy(dst + (size_t)j * ld, U + (size_t)(p.c0 + j) * lm + p.r0, sizeof(T) * p.nr);
     } else { // (U V)^T = V^T U^T : the U-role is V^T (n_leaf x r), V is r x n_leaf with ld r
         const T *V = (const T *)f.b[l];
         const int r = v.r;
         for (int j = 0; j < p.nc; j++)
             for (int i = 0; i < p.nr; i++)
-                dst[(size_t)j * p.nr + i] = conj_if(V[(size_t)(p.r0 + i) * r + (p.c0 + j)], v.conj);
+                dst[(size_t)j * ld + i] = conj_if(V[(size_t)(p.r0 + i) * r + (p.c0 + j)], v.conj);
     }
 }
 
@@ -625,7 +686,7 @@ static void fill_tile1(const hmb200_flat &f, const VLeaf &v, const Piece1 &p, T 
 
 template <typename T>
 static void pack_stages_t(const hmb200_flat &f, const Plan &plan, int phase, size_t s0, size_t s1, uint8_t *dst) {
-    const PhasePlan &ph = phase == 1 ? plan.phase1 : (phase == 2 ? plan.phase2 : plan.phase1m);
+    const PhasePlan &ph = phase == 1 ? plan.phase1 : plan.phase2;
     const uint64_t base = ph.stages[s0].gmem_off;
 #pragma omp parallel for schedule(dynamic, 16)
     for (int64_t s = (int64_t)s0; s < (int64_t)s1; s++) {
@@ -652,16 +713,6 @@ static void pack_stages_t(const hmb200_flat &f, const Plan &plan, int phase, siz
                 d.pad = (uint16_t)((32768 + p.lr - 1) / p.lr);     // lane / lr == (lane * pad) >> 15 for lane < 32, lr <= 32
                 fill_tile1<T>(f, plan.vleaves[p.vleaf], p, tile, p.lr);
                 if (((size_t)p.lr * p.nq * sizeof(T)) & 15) std::memset(tile + (size_t)p.lr * p.nq, 0, 8);
-            } else if (phase == 3) { // multi-RHS phase 1: a stack of sub-pieces sharing their columns, ld = total rows
-                const MmTile &t = plan.mm_tiles[pi];
-                d.out_off = t.out_row; d.nc = t.nq; d.nr = (uint8_t)t.rows; d.ro = 0; d.pad = 0;
-                int roff = 0;
-                for (uint32_t q = 0; q < t.n_sub; q++) {
-                    const Piece1 &p = plan.pieces1m[t.first_sub + q];
-                    fill_tile1<T>(f, plan.vleaves[p.vleaf], p, tile + roff, t.rows);
-                    roff += p.lr;
-                }
-                if (((size_t)t.rows * t.nq * sizeof(T)) & 15) std::memset(tile + (size_t)t.rows * t.nq, 0, 8);
             } else {
                 const Piece2 &p = plan.pieces2[pi];
                 d.out_off = 0; d.nc = (uint16_t)p.nc; d.nr = (uint8_t)p.nr; d.ro = (uint8_t)p.ro;
@@ -677,8 +728,69 @@ static void pack_stages_t(const hmb200_flat &f, const Plan &plan, int phase, siz
     }
 }
 
+// multi-RHS panel packets: the packet's pieces are laid into a zero-filled column-major panel, which is then written out
+// fragment-major (plan.h): chunk (kg, mt), lane = 4 gid + tig  <-  A[8 mt + gid][kg_cols kg + tig] (+ 4 for the second half, real)
+template <typename T>
+static void pack_mm_t(const hmb200_flat &f, const Plan &plan, int phase, size_t s0, size_t s1, uint8_t *dst) {
+    const MmPhasePlan &ph = phase == 3 ? plan.mm1 : plan.mm2;
+    const uint64_t base   = ph.stages[s0].gmem_off;
+    constexpr int KG      = sizeof(T) == 8 ? 8 : 4;
+#pragma omp parallel
+    {
+        std::vector<T> panel;
+#pragma omp for schedule(dynamic, 16)
+        for (int64_t s = (int64_t)s0; s < (int64_t)s1; s++) {
+            const StageEntry &se   = ph.stages[s];
+            const MmPacketHost &pk = ph.packets[s];
+            uint8_t *out           = dst + (se.gmem_off - base);
+            const int mt_panel = (pk.rows + 7) / 8, ldp = mt_panel * 8, ncol = (int)pk.n_kg * KG;
+            MmPacketHeader h{};
+            h.n_kg = pk.n_kg; h.out0 = pk.out0; h.rows = pk.rows; h.mt_panel = (uint16_t)mt_panel; h.flags = pk.flags;
+            const uint32_t a_bytes = pk.n_kg * (uint32_t)mt_panel * 512u;
+            h.map_off16 = pk.map_first != UINT32_MAX ? (uint16_t)((16 + a_bytes) / 16) : 0;
+            std::memcpy(out, &h, 16);
+            panel.assign((size_t)ldp * std::max(ncol, 1), T(0));
+            for (uint32_t i = 0; i < pk.n_pieces; i++) {
+                const MmPiece &mp = ph.pieces[pk.first_piece + i];
+                const VLeaf &v    = plan.vleaves[mp.vleaf];
+                T *at             = panel.data() + (size_t)mp.kcol * ldp + mp.ro;
+                if (phase == 3) fill_tile1<T>(f, v, Piece1{mp.vleaf, mp.r0, mp.nr, mp.c0, mp.nc, 0}, at, ldp);
+                else fill_tile2<T>(f, v, Piece2{mp.vleaf, mp.r0, mp.nr, mp.c0, mp.nc, mp.ro, 0}, at, ldp);
+            }
+            T *chunks = reinterpret_cast<T *>(out + 16);
+            for (uint32_t kg = 0; kg < pk.n_kg; kg++)
+                for (int mt = 0; mt < mt_panel; mt++) {
+                    T *c = chunks + ((size_t)kg * mt_panel + mt) * (512 / sizeof(T));
+                    for (int lane = 0; lane < 32; lane++) {
+                        const int gid = lane >> 2, tig = lane & 3;
+                        const T *src  = panel.data() + (size_t)(kg * KG + tig) * ldp + 8 * mt + gid;
+                        if (sizeof(T) == 8) {
+                            c[2 * lane]     = src[0];
+                            c[2 * lane + 1] = src[(size_t)4 * ldp];
+                        } else {
+                            c[lane] = src[0];
+                        }
+                    }
+                }
+            if (pk.map_first != UINT32_MAX) {
+                uint8_t *m = out + 16 + a_bytes;
+                std::memset(m, 0, align_up((uint32_t)pk.rows * 4, 16));
+                std::memcpy(m, plan.mm_row_map.data() + pk.map_first, (size_t)pk.rows * 4);
+            }
+            uint64_t end = se.gmem_off + se.bytes;
+            uint64_t nxt = (s + 1 < (int64_t)ph.stages.size()) ? ph.stages[s + 1].gmem_off : ph.stream_bytes;
+            if (nxt > end && s + 1 <= (int64_t)s1) std::memset(out + se.bytes, 0, (size_t)std::min<uint64_t>(nxt - end, 128));
+        }
+    }
+}
+
 void pack_stages(const hmb200_flat &f, const Plan &plan, int phase, size_t s0, size_t s1, uint8_t *dst) {
     if (s1 <= s0) return;
+    if (phase >= 3) {
+        if (plan.elem_bytes == 8) pack_mm_t<double>(f, plan, phase, s0, s1, dst);
+        else pack_mm_t<std::complex<double>>(f, plan, phase, s0, s1, dst);
+        return;
+    }
     if (plan.elem_bytes == 8)
         pack_stages_t<double>(f, plan, phase, s0, s1, dst);
     else

@@ -22,12 +22,10 @@ struct Options {
     int ctas           = 0;
     int build_transpose = 0;
     // multi-RHS (DMMA) path
-    int build_matmat    = 1;     // also pack the phase-1 stream of the multi-RHS kernels
-    int stage_z_elems   = 112;   // max operand elements (x / t entries) a phase-2 packet may reference: the multi-RHS kernel
-                                 // stages stage_z_elems x (mu + pad) operand ROWS per packet
-    int mm_stage_bytes  = 40960; // packet size of the multi-RHS phase-1 stream
-    int mm_bin_cols     = 128;
-    int mm_variant      = 1;     // bit 0 / bit 1: register-double-buffered DMMA fragments in multi-RHS phase 1 / phase 2   // columns of a source bin (the slice of X kept resident in shared memory)
+    int build_matmat    = 1;     // also pack the two panel streams of the multi-RHS kernels
+    int mm1_kg          = 4;     // k-groups (8 columns real / 4 complex) per phase-1 packet: 128 rows x 32 columns = 32 KiB
+    int mm2_kg          = 7;     // k-groups per phase-2 packet: 64 rows x 56 columns = 28 KiB
+    int mm_task_cols    = 1024;  // columns of a phase-1 unit; wider source clusters are split and their partial T rows summed
 };
 Options resolve_options(const hmb200_options *opt);
 
@@ -53,10 +51,27 @@ struct Piece2 { // U-role / dense tile rows [r0,r0+nr) x cols [c0,c0+nc) of the 
     uint32_t z_src; // xz element the tile's first column multiplies
 };
 
-struct MmTile { // multi-RHS phase-1 tile: sub-pieces [first_sub, first_sub + n_sub) of pieces1m stacked row-wise
-    uint32_t first_sub, n_sub;
-    uint32_t out_row; // first workspace row of its `rows` output rows
-    uint16_t rows, nq, zrow;
+struct MmPiece { // part of a view placed in a panel packet: panel rows [ro, ro+nr) x packet columns [kcol, kcol+nc)
+    int32_t vleaf;
+    int32_t r0, nr; // rows of the role matrix (phase 1: rows of V, phase 2: rows of U / of the dense view)
+    int32_t c0, nc; // columns of the role matrix
+    int32_t ro;     // first panel row
+    int32_t kcol;   // first column inside the packet
+};
+struct MmPacketHost { // planner-side description of a multi-RHS packet
+    uint32_t first_piece, n_pieces;
+    uint32_t n_kg, out0;
+    uint16_t rows, flags;
+    uint32_t map_first; // phase 1, last packet: first entry of mm_row_map (rows entries)
+};
+struct MmPhasePlan {
+    std::vector<StageEntry> stages;
+    std::vector<MmPacketHost> packets;
+    std::vector<MmPiece> pieces;
+    std::vector<ZCopy> zcopies; // src_elem = workspace row, bytes = rows * elem_bytes, dst_off = z-area row * elem_bytes
+    std::vector<WorkUnit> units;
+    uint64_t stream_bytes = 0;
+    uint32_t max_packet_bytes = 0, max_z_rows = 0;
 };
 
 struct StageHost { // planner-side description of a packet
@@ -86,16 +101,15 @@ struct Plan {
     std::vector<Piece2> pieces2;
     PhasePlan phase1, phase2;
     std::vector<ReduceSeg> reduce;
-    // multi-RHS phase 1 (T_j = V_j X): V tiles grouped by SOURCE bin; the bin's rows of X stay resident in shared memory
-    // while its tiles stream.  Leaves wider than a bin produce partial T rows (workspace rows >= xz_elems) summed by
-    // reduce_mm; piece_zoff = first row of the tile's columns inside the resident X slice.
-    std::vector<int32_t> src_bin_start; // n_src_bins + 1
-    std::vector<Piece1> pieces1m;        // sub-pieces; out_off = workspace row of the sub-piece's first output row
-    std::vector<MmTile> mm_tiles;        // the packed tiles (the `pieces` of phase1m)
+    // multi-RHS path (plan.h, "mm streams"): workspace ROWS [ x (n_in) | T (sum of ranks, tight, view order) | partial T rows
+    // of split phase-1 units | kMmZeroRows zero rows ]
+    MmPhasePlan mm1, mm2;
+    std::vector<uint32_t> mm_t_row;       // per view: first workspace row of its T (low-rank views)
+    std::vector<uint32_t> mm_row_map;     // phase 1: destination workspace row of every panel row of every unit
     std::vector<uint32_t> reduce_mm_rows; // part rows of the segments: seg.first_partial indexes this array
-    PhasePlan phase1m;
-    std::vector<ReduceSeg> reduce_mm;   // in workspace ROWS
-    uint64_t mm_rows = 0;               // workspace rows of the multi-RHS path: [x | t | (matvec partials) | mm partials]
+    std::vector<ReduceSeg> reduce_mm;     // in workspace ROWS: final row, first entry of reduce_mm_rows, parts, rows
+    uint64_t mm_rows = 0;                 // workspace rows in total
+    uint32_t mm_zero_row = 0;             // first of the zero rows
     uint64_t xz_elems = 0; // x | t | partials (+ padding)
     uint32_t t_begin  = 0; // first element of the t region
     double stored_coefficients = 0;
@@ -104,7 +118,7 @@ struct Plan {
 // builds the schedule for out = op(A) in ; throws std::runtime_error on invalid input
 void build_plan(const hmb200_flat &flat, int elem_bytes, char op, const Options &opt, Plan &plan);
 
-// fills packets [stage_begin, stage_end) of phase `phase` (1 or 2) into dst, where dst corresponds to stream offset
+// fills packets [stage_begin, stage_end) of phase `phase` (1 or 2; 3 / 4 = the multi-RHS panel streams mm1 / mm2) into dst, where dst corresponds to stream offset
 // plan.phaseN.stages[stage_begin].gmem_off.  T is double or std::complex<double> (selected by plan.elem_bytes).
 void pack_stages(const hmb200_flat &flat, const Plan &plan, int phase, size_t stage_begin, size_t stage_end, uint8_t *dst);
 

@@ -397,8 +397,61 @@ class B200DistributedOperator:
         self.engine.add_vector_product(trans, alpha, x_local, 0.0, full)
         return exchange_sum_slabs_(full, self.offs, self.sizes, y_local, beta, self.group if torch.distributed.is_initialized() else None)
 
+    def _setup_fused_matmat(self, mu: int):
+        """replicated (n_target x mu) blocks in a second peer-mapped region (hmb200_peer_mm_create / _attach); collective"""
+        import ctypes
+
+        import torch.distributed as dist
+
+        lib = _lib.lib()
+        handle = (ctypes.c_ubyte * 64)()
+        ok = lib.hmb200_peer_mm_create(self.engine._h, int(mu), handle) == 0
+        err = "" if ok else _lib.last_error()
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle) if ok else None, group=self.group)
+        if ok and all(hd is not None for hd in handles):
+            blob = (ctypes.c_ubyte * (64 * self.world)).from_buffer_copy(b"".join(handles))
+            ok = lib.hmb200_peer_mm_attach(self.engine._h, blob) == 0
+            err = "" if ok else _lib.last_error()
+        else:
+            ok = False
+        flags = [None] * self.world
+        dist.all_gather_object(flags, ok, group=self.group)
+        if not all(flags):
+            raise RuntimeError(f"hmb200: replicated multi-RHS blocks could not be shared between the ranks ({err or 'a peer failed'})")
+        bufs = []
+        for i in range(2):
+            ptr = ctypes.c_void_p()
+            _lib.check(lib.hmb200_peer_mm_buffer(self.engine._h, i, ctypes.byref(ptr)))
+            bufs.append(_device_tensor(ptr.value, self.n_target * mu, self.is_complex, self.device))
+        self._mm_ybuf = {b.data_ptr(): b for b in bufs}
+        self._mm_mu = int(mu)
+
+    def matmat_cluster_fused_(self, X_cluster, mu: int):
+        """returns the replicated Y = A X (row-major n_target x mu, cluster numbering) as a view of one of the operator's two
+        peer-mapped blocks: the multi-RHS slab product stores every bin's rows into the block of every rank from its epilogue
+        (no NCCL call).  Collective; the returned tensor stays valid until the product after the next."""
+        import ctypes
+
+        if not self.fused:
+            raise RuntimeError("fused all-gather is not set up on this operator")
+        if self._peer_failed:
+            self.check_peers()
+        if getattr(self, "_mm_mu", 0) != int(mu):
+            self._setup_fused_matmat(mu)
+        px, _ = self.engine._ptr(X_cluster, self.n_source * mu, False)
+        out = ctypes.c_void_p()
+        one = (ctypes.c_double * 2)(1.0, 0.0)
+        fn = _lib.lib().hmb200_matrix_product_allgather_z if self.is_complex else _lib.lib().hmb200_matrix_product_allgather_d
+        _lib.check(fn(self.engine._h, one, px, int(mu), ctypes.byref(out)))
+        return self._mm_ybuf[out.value]
+
     def matmat_cluster_(self, X_cluster, Y_cluster, mu: int):
-        """row-major (n x mu) blocks (add_distributed_operator_matrix_product_row_major_global_to_global.hpp:18-84)."""
+        """row-major (n x mu) blocks (add_distributed_operator_matrix_product_row_major_global_to_global.hpp:18-84): slab product +
+        all-gather of the rows, fused into the kernel when the peer regions are set up.  Returns the replicated block (a view of
+        the operator's own buffer on the fused path, `Y_cluster` otherwise)."""
+        if self.fused and self.world > 1 and self.engine.info["mm_stream_bytes"] > 0:
+            return self.matmat_cluster_fused_(X_cluster, mu)
         o, s = self.offs[self.rank], self.sizes[self.rank]
         self.engine.add_matrix_product_row_major("N", 1.0, X_cluster, 0.0, Y_cluster.view(-1)[o * mu:(o + s) * mu], mu)
         return allgather_slabs_(Y_cluster, self.offs, self.sizes, mu, self.group)
@@ -542,18 +595,18 @@ class B200DistributedOperator:
         mu = X.shape[1]
         (xu, xc, yc, yu), (pin_x, pin_y) = self._buffers(mu)
         with torch.cuda.device(self.device):
-            # host side of the reference does per-column permutation + transpose to row-major (:176-187); here the
-            # column-major block is permuted on the device and transposed by a strided view copy
+            # host side of the reference does per-column permutation + transposes to row-major and back (:176-187, :202-204);
+            # here both are one layout kernel each (hmb200_block_to_rows / hmb200_rows_to_block, permutation fused)
             pin_x.numpy()[:] = np.asfortranarray(X, dtype=self.np_dtype).reshape(-1, order="F")
             xu.copy_(pin_x, non_blocking=True)
-            self._permute(True, self.perm_s, self.n_source, xu, xc, mu)    # column-major, per column
-            xr = xc.view(mu, self.n_source).t().contiguous()               # -> row-major n x mu
-            yr = yu.view(self.n_target, mu)
-            self.matmat_cluster_(xr.view(-1), yr, mu)
-            yc.view(mu, self.n_target).copy_(yr.t())                        # back to column-major
-            self._permute(False, self.perm_t, self.n_target, yc, yu, mu)
+            st = torch.cuda.current_stream(self.device).cuda_stream
+            lib = _lib.lib()
+            _lib.check(lib.hmb200_block_to_rows(self.perm_s.data_ptr(), self.n_source, mu, xu.data_ptr(), self.n_source, xc.data_ptr(), self.es, st))
+            yr = self.matmat_cluster_(xc, yc.view(self.n_target, mu), mu)
+            _lib.check(lib.hmb200_rows_to_block(self.perm_t.data_ptr(), self.n_target, mu, yr.data_ptr(), yu.data_ptr(), self.n_target, self.es, st))
             pin_y.copy_(yu, non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
+        self.check_peers()
         return np.array(pin_y.numpy().reshape((self.n_target, mu), order="F"), order="F")
 
     def close(self):

@@ -342,7 +342,7 @@ class CudaKrylovSpace:
         self._hpin, self._hev = None, None
         self._k_max = 0
         self._blk = {}
-        self.mm_min_cols = 5  # narrowest block that goes through the multi-RHS (DMMA) product, see matmat
+        self.mm_min_cols = 2  # narrowest block that goes through the multi-RHS (DMMA) product (1 = a plain matvec)
         self.kernel_launches = 0
 
     def _check_peers(self):
@@ -443,9 +443,6 @@ class CudaKrylovSpace:
 
         mu = int(vin.shape[0])
         if mu < self.mm_min_cols:
-            # a pass of the DMMA kernel costs about the same for 2 as for 32 right-hand sides (profiles/r01_block_gmres_profile.log:
-            # ~10 ms at N=1M against 2.4 ms for the single-RHS stream kernel), so very narrow blocks take the streamed product
-            # per column (same values to rounding, same number of block operator calls)
             for c in range(mu):
                 self.matvec(vin[c], vout[c])
             return
@@ -454,11 +451,13 @@ class CudaKrylovSpace:
                              self.torch.empty(self.n_local * mu, dtype=self.dtype, device=self.device))
         xr, yr = self._blk[mu]
         with self.torch.cuda.device(self.device):
-            xr.view(self.n_global, mu)[self.off:self.off + self.n_local].copy_(vin.t())  # column blocks -> row-major slab
+            # column blocks (mu, n_local) <-> row-major slab rows: one layout kernel each way (hmb200_block_to_rows / rows_to_block)
+            _lib.check(self.lib.hmb200_block_to_rows(None, self.n_local, mu, vin.data_ptr(), self.n_local, xr.data_ptr() + self.es * mu * self.off, self.es, self._stream()))
             if self.world > 1:
                 allgather_slabs_(xr, self.op.offs, self.op.sizes, mu, self.group)
             self.op.engine.add_matrix_product_row_major("N", 1.0, xr, 0.0, yr, mu)
-            vout.copy_(yr.view(self.n_local, mu).t())
+            _lib.check(self.lib.hmb200_rows_to_block(None, self.n_local, mu, yr.data_ptr(), vout.data_ptr(), self.n_local, self.es, self._stream()))
+            self.kernel_launches += 2
 
     # ---- reductions ---------------------------------------------------------------------------------------------
     def allreduce_many(self, handles):

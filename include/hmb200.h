@@ -66,13 +66,13 @@ typedef struct hmb200_options {
     int32_t unit_stages;     /* phase-1 stages per work unit (default 32) */
     int32_t ctas;            /* persistent CTAs (default: number of SMs) */
     int32_t build_transpose; /* also pack the transposed operator so trans='T'/'C' products work (default 0) */
-    int32_t no_matmat;       /* 1: do not pack the multi-RHS phase-1 stream (saves ~35 % device memory; the multi-RHS
-                                entry points then fall back to one streamed product per right-hand side) */
-    int32_t stage_z_elems;   /* max operand entries (x / t) a phase-2 packet references (default 112); the multi-RHS kernel
-                                stages that many operand ROWS of (mu + pad) per packet */
-    int32_t mm_stage_bytes;  /* packet bytes of the multi-RHS phase-1 stream (default 40960) */
-    int32_t mm_bin_cols;     /* entries of x per source bin, resident in shared memory in multi-RHS phase 1 (default 128) */
-    int32_t mm_variant;      /* tuning: 1 + bitmask (bit 0 / 1: double-buffered DMMA fragments in multi-RHS phase 1 / 2; bit 2: EXPERIMENTAL plain-DFMA consumer, csrc/kernels/mmf_kernels.cuh); 0 = default */
+    int32_t no_matmat;       /* 1: do not pack the two panel streams of the multi-RHS kernels (halves the device memory; the
+                                multi-RHS entry points then fall back to one streamed product per right-hand side) */
+    int32_t mm_task_cols;    /* multi-RHS phase 1: source columns per work unit (default 1024); wider clusters are split and their
+                                partial T rows summed */
+    int32_t mm1_kg;          /* multi-RHS phase 1: k-groups (8 columns real / 4 complex) per packet of a 128-row panel (default 4) */
+    int32_t mm2_kg;          /* multi-RHS phase 2: k-groups per packet of a 64-row panel (default 7) */
+    int32_t reserved0;
     int32_t reserved[1];
 } hmb200_options;
 
@@ -147,6 +147,18 @@ int hmb200_peer_create(hmb200_handle *h, int n_ranks, int rank, int64_t n_global
 int hmb200_peer_attach(hmb200_handle *h, const unsigned char *ipc_handles);
 int hmb200_peer_buffer(hmb200_handle *h, int index, void **ptr);
 int hmb200_peer_status(hmb200_handle *h, int *err);
+/* the same for row-major blocks of mu right-hand sides (MPI_Allgatherv of
+ * core/distributed_operator/linalg/add_distributed_operator_matrix_product_row_major_global_to_global.hpp:75): a second shared region
+ * per rank holding two replicated (n_global x mu) blocks.  hmb200_peer_mm_create after hmb200_peer_create (again for another
+ * mu: the old blocks are released), exchange the handles, hmb200_peer_mm_attach; then, collectively,
+ * hmb200_matrix_product_allgather_{d,z}(h, alpha, in (device, n_cols x mu row-major), mu, &Y): Y (device pointer into this
+ * rank's region, n_global x mu row-major, cluster numbering) = alpha * A * in on all ranks -- the bin epilogue of the multi-RHS
+ * kernel stores every tile row to all ranks, same epoch flags; counts as one collective of the sequence above. */
+int hmb200_peer_mm_create(hmb200_handle *h, int mu, unsigned char *ipc_handle_out);
+int hmb200_peer_mm_attach(hmb200_handle *h, const unsigned char *ipc_handles);
+int hmb200_peer_mm_buffer(hmb200_handle *h, int index, void **ptr);
+int hmb200_matrix_product_allgather_d(hmb200_handle *h, const double *alpha, const double *in, int mu, void **y_replicated);
+int hmb200_matrix_product_allgather_z(hmb200_handle *h, const double *alpha, const double *in, int mu, void **y_replicated);
 /* the solver's two collectives on the same peer regions (no NCCL / MPI on the iteration path):
  *   hmb200_peer_allgather     local slab (n_rows elements, device) -> replicated vector on every rank
  *                             (MPI_Allgatherv of ..._vector_product_local_to_local.hpp:44); counts as one collective of step 3
@@ -204,6 +216,13 @@ int hmb200_kernel_ms_avg(hmb200_handle *h, float ms[4], int *n_products);
 int hmb200_enable_timing(hmb200_handle *h, int on);
 /* number of kernel launches issued by this handle since creation */
 int64_t hmb200_launch_count(const hmb200_handle *h);
+/* Layout change between the reference's COLUMN-major blocks in user numbering (row i, rhs j at i + j*col_stride) and the row-major
+ * blocks in cluster numbering of the operator interface (cluster row i, rhs j at i*mu + j), fused with the permutation (perm:
+ * device pointer, cluster slot -> user index, or NULL for none): the per-column user_to_cluster / cluster_to_user plus the
+ * transposes of core/hmatrix/linalg/add_hmatrix_matrix_product.hpp:29-31,190-204 and of HPDDMOperator::GMV
+ * (core/wrappers/wrapper_hpddm.hpp:108-116,129-135).  Device pointers, asynchronous on `stream`. */
+int hmb200_block_to_rows(const int32_t *perm, int n, int mu, const void *src_colmajor, long long col_stride, void *dst_rowmajor, int elem_bytes, void *stream);
+int hmb200_rows_to_block(const int32_t *perm, int n, int mu, const void *src_rowmajor, void *dst_colmajor, long long col_stride, int elem_bytes, void *stream);
 /* Diagnostics: measured FP64 issue rates of `device` in TFLOP/s -- tensor-core DMMA (mma.sync.m8n8k4.f64) and plain DFMA, 8
  * warps per SM with 8 independent accumulators each; the roofline denominators of the multi-RHS path (no reference
  * counterpart: bench.py reports them next to the achieved rate). */

@@ -164,23 +164,6 @@ def bridge_available():
         return False
 
 
-def emulate_mmf(flat, op, alpha, X, beta, Y, **opts):
-    """the same product with the work split of the experimental DFMA consumer (kernels/mmf_kernels.cuh), lane by lane"""
-    emu = emulator()
-    o = _lib.hmb200_options()
-    for k, v in opts.items():
-        setattr(o, k, v)
-    cs = flat.c_struct()
-    a = (ctypes.c_double * 2)(complex(alpha).real, complex(alpha).imag)
-    b = (ctypes.c_double * 2)(complex(beta).real, complex(beta).imag)
-    X = np.ascontiguousarray(X, dtype=flat.np_dtype)
-    assert Y.flags.c_contiguous and Y.dtype == flat.np_dtype
-    rc = emu.plan_emulate_mmf(ctypes.byref(cs), flat.elem_bytes, ctypes.c_char(op.encode()), ctypes.byref(o), a,
-                              ctypes.c_void_p(X.ctypes.data), b, ctypes.c_void_p(Y.ctypes.data), int(X.shape[1]))
-    if rc:
-        raise RuntimeError(emu.plan_emulate_error().decode())
-
-
 def emulate_mm(flat, op, alpha, X, beta, Y, **opts):
     """Y = beta*Y + alpha*op(A)*X (row-major n x mu) through the multi-RHS packet streams, on the CPU."""
     emu = emulator()
@@ -197,5 +180,5 @@ def emulate_mm(flat, op, alpha, X, beta, Y, **opts):
                              ctypes.c_void_p(X.ctypes.data), b, ctypes.c_void_p(Y.ctypes.data), int(X.shape[1]), stats)
     if rc:
         raise RuntimeError(emu.plan_emulate_error().decode())
-    keys = ("stream1m_bytes", "stream2_bytes", "pieces1m", "pieces2", "stages1m", "stages2", "reduce_mm", "src_bins", "mm_rows", "stored")
+    keys = ("mm1_bytes", "mm2_bytes", "pieces_mm1", "pieces_mm2", "stages_mm1", "stages_mm2", "reduce_mm", "units_mm1", "mm_rows", "stored", "zcopies_mm1", "zcopies_mm2")
     return dict(zip(keys, list(stats)))

@@ -67,12 +67,12 @@ std::map<std::string, double> check(uintptr_t address, int device, int mu, const
     const std::string ops = !with_transpose ? "N" : (std::is_same<T, double>::value ? "NT" : (sfl == 'S' ? "NT" : (sfl == 'H' ? "NC" : "NTC")));
     for (char trans : ops) {
         const int ni = trans == 'N' ? ns : nt, no = trans == 'N' ? nt : ns;
-        std::vector<T> x(ni), y0(no), y1, y2, work(std::max(nt, ns) * 2);
+        std::vector<T> x(ni), y0(no), y1, y2;
         for (auto &v : x) v = rnd<T>(gen);
         for (auto &v : y0) v = rnd<T>(gen);
         y1 = y0; y2 = y0;
-        add_distributed_operator_vector_product_global_to_global(trans, alpha, d_ref, x.data(), beta, y1.data(), work.data());
-        add_distributed_operator_vector_product_global_to_global(trans, alpha, d_gpu, x.data(), beta, y2.data(), work.data());
+        add_distributed_operator_vector_product_global_to_global(trans, alpha, d_ref, x.data(), beta, y1.data(), (T *)nullptr); // work == nullptr: the drivers allocate their own buffers
+        add_distributed_operator_vector_product_global_to_global(trans, alpha, d_gpu, x.data(), beta, y2.data(), (T *)nullptr);
         res[std::string("vector_global_to_global_") + trans] = rel_diff(y2, y1);
     }
     // ---- global-to-global matrix product, row-major blocks stored as (mu x n) Matrix (..._row_major_global_to_global.hpp:18) ----
@@ -80,9 +80,8 @@ std::map<std::string, double> check(uintptr_t address, int device, int mu, const
         Matrix<T> X(mu, ns), Y1(mu, nt), Y2(mu, nt);
         for (int i = 0; i < mu * ns; i++) X.data()[i] = rnd<T>(gen);
         for (int i = 0; i < mu * nt; i++) Y1.data()[i] = Y2.data()[i] = rnd<T>(gen);
-        std::vector<T> work((size_t)std::max(nt, ns) * mu * 2);
-        internal_add_distributed_operator_matrix_product_row_major_global_to_global('N', alpha, d_ref, X, beta, Y1, work.data());
-        internal_add_distributed_operator_matrix_product_row_major_global_to_global('N', alpha, d_gpu, X, beta, Y2, work.data());
+        internal_add_distributed_operator_matrix_product_row_major_global_to_global('N', alpha, d_ref, X, beta, Y1, (T *)nullptr);
+        internal_add_distributed_operator_matrix_product_row_major_global_to_global('N', alpha, d_gpu, X, beta, Y2, (T *)nullptr);
         std::vector<T> a(Y2.data(), Y2.data() + (size_t)mu * nt), b(Y1.data(), Y1.data() + (size_t)mu * nt);
         res["matrix_row_major_global_to_global_N"] = rel_diff(a, b);
     }
@@ -110,11 +109,11 @@ std::map<std::string, double> check(uintptr_t address, int device, int mu, const
         std::string args = hpddm_args;
         opt.parse(args, false);
         for (int m : {1, mu}) {
-            std::vector<T> xs((size_t)ns * m), rhs((size_t)nt * m), x1((size_t)ns * m, T(0)), x2((size_t)ns * m, T(0)), work(std::max(nt, ns) * 2);
+            std::vector<T> xs((size_t)ns * m), rhs((size_t)nt * m), x1((size_t)ns * m, T(0)), x2((size_t)ns * m, T(0));
             for (auto &v : xs) v = rnd<T>(gen);
             for (int c = 0; c < m; c++) {
                 std::fill_n(rhs.data() + (size_t)c * nt, nt, T(0));
-                add_distributed_operator_vector_product_global_to_global('N', T(1), d_ref, xs.data() + (size_t)c * ns, T(0), rhs.data() + (size_t)c * nt, work.data());
+                add_distributed_operator_vector_product_global_to_global('N', T(1), d_ref, xs.data() + (size_t)c * ns, T(0), rhs.data() + (size_t)c * nt, (T *)nullptr);
             }
             DDMSolverBuilder<T, double> b_ref(d_ref, H), b_gpu(d_gpu, H); // block-Jacobi builder, never factorised (-hpddm_schwarz_method none)
             b_ref.solver.solve(rhs.data(), x1.data(), m);

@@ -261,6 +261,17 @@ def _dist_worker(rank, world, port, q, kernel="laplace_reg"):
         same = all(np.array_equal(v, y) for v in ys)
         op_nccl = B200DistributedOperator(slab, tree.partition, fused_allgather=False)
         same = same and np.array_equal(op_nccl * x, y) and not op_nccl.fused
+        # the same for blocks: the multi-RHS bin epilogue stores the rows to every rank (two alternating replicated blocks);
+        # a second width forces the blocks to be re-created, 70 columns take two passes with a column tail
+        same = same and all(np.array_equal(op @ X, Y) for _ in range(3)) and np.array_equal(op_nccl @ X, Y)
+        X70 = np.asfortranarray(helpers.rand_vec(rng, n, dt, 70))
+        Y70 = op @ X70
+        same = same and np.array_equal(op_nccl @ X70, Y70) and np.array_equal(op @ X, Y)
+        # node-shared page-locked result vector: every rank downloads 1/P of y; all ranks see the same bits
+        if world > 1 and op.fused:
+            for _ in range(3):
+                same = same and np.array_equal(np.array(op.matvec(x, out="shared")), y)
+            same = same and getattr(op, "_shm", None) is not None
         status = op.peer_status() if op.fused else 0
         # transposed / conjugate-transposed distributed product: sum over the ranks of op(A_p) x_p (all-reduce driver)
         import torch
@@ -437,29 +448,9 @@ def test_local_to_local_drivers_two_gpus():
         assert max(errs) < TOL, (rank, errs)
 
 
-@pytest.mark.skipif(not __import__("os").environ.get("HMB200_TEST_EXPERIMENTAL"), reason="experimental kernels: set HMB200_TEST_EXPERIMENTAL=1")
-@pytest.mark.parametrize("name,mu", [("d_N_cylinder", 8), ("d_N_cylinder", 64), ("d_N_rect", 37), ("d_SL_cylinder", 17), ("z_N_sphere", 5), ("z_HL_cylinder", 40)])
-def test_multi_rhs_dfma_experimental(name, mu):
-    """the plain-DFMA multi-RHS consumer (csrc/kernels/mmf_kernels.cuh, Options.mm_variant bit 2) vs the oracle; its index
-    arithmetic is checked on the CPU by tests/test_planner_emulated.py::test_dfma_consumer_mapping_*; not in the default suite
-    until it has run on a GPU"""
-    flat, _ = load_golden(name)
-    rng = np.random.default_rng(mu)
-    e = _engine(flat, build_transpose=1, mm_variant=1 + 4)
-    alpha, beta = (1.25, -0.75) if flat.dtype == "d" else (1.25 - 0.5j, 0.3 + 0.9j)
-    for op in _ops_of(flat):
-        n_in, n_out = (flat.n_cols, flat.n_rows) if op == "N" else (flat.n_rows, flat.n_cols)
-        X = np.ascontiguousarray(helpers.rand_vec(rng, n_in, flat.np_dtype, mu))
-        Y0 = np.ascontiguousarray(helpers.rand_vec(rng, n_out, flat.np_dtype, mu))
-        Y_ref = Y0.copy()
-        fo.add_matrix_product_row_major(flat, op, alpha, X, beta, Y_ref, mu)
-        Y = Y0.copy()
-        e.add_matrix_product_row_major(op, alpha, X, beta, Y, mu)
-        assert rel_err(Y, Y_ref) < TOL, (op, rel_err(Y, Y_ref))
-    e.close()
-
-
-@pytest.mark.parametrize("name,mu", [("d_N_cylinder", 64), ("d_N_rect", 70), ("d_SL_cylinder", 17), ("z_N_sphere", 32), ("z_HL_cylinder", 40), ("z_SL_sphere", 5)])
+@pytest.mark.parametrize("name,mu", [("d_N_cylinder", 64), ("d_N_rect", 70), ("d_SL_cylinder", 17), ("z_N_sphere", 32), ("z_HL_cylinder", 40), ("z_SL_sphere", 5),
+                                     ("d_N_cylinder", 2), ("d_N_rect", 8), ("d_N_cylinder", 12), ("d_N_rect", 30), ("d_SU_sphere", 33), ("z_N_sphere", 3), ("z_N_sphere", 12),
+                                     ("z_HU_sphere", 20)])
 def test_multi_rhs_dmma(name, mu):
     """Y = beta*Y + alpha*op(A)*X on the DMMA kernels (several passes, padded column tails) vs the oracle, and the
     user-numbering `@` with fused permutations vs the per-column path (no_matmat)."""
@@ -488,6 +479,26 @@ def test_multi_rhs_dmma(name, mu):
     assert Yu.flags.f_contiguous and rel_err(Yu, Yu2) < TOL
     e.close()
     e2.close()
+
+
+@pytest.mark.parametrize("name,mu", [("d_N_cylinder", 64), ("d_N_rect", 9), ("z_N_sphere", 32), ("z_HL_cylinder", 6)])
+@pytest.mark.parametrize("opts", [dict(mm_task_cols=40, mm1_kg=2, mm2_kg=3, bin_rows=20), dict(mm_task_cols=8, mm1_kg=1, mm2_kg=1, bin_rows=9), dict(mm1_kg=6, mm2_kg=12)])
+def test_multi_rhs_dmma_split_units(name, mu, opts):
+    """the multi-RHS kernels on schedules with split phase-1 units (partial T rows + reduce_rows_kernel), short and long packets,
+    small bins (panels with few m-tiles) vs the oracle"""
+    flat, _ = load_golden(name)
+    rng = np.random.default_rng(mu)
+    e = _engine(flat, build_transpose=1, **opts)
+    alpha, beta = (1.25, -0.75) if flat.dtype == "d" else (1.25 - 0.5j, 0.3 + 0.9j)
+    for op in _ops_of(flat):
+        n_in, n_out = (flat.n_cols, flat.n_rows) if op == "N" else (flat.n_rows, flat.n_cols)
+        X = np.ascontiguousarray(helpers.rand_vec(rng, n_in, flat.np_dtype, mu))
+        Y = np.ascontiguousarray(helpers.rand_vec(rng, n_out, flat.np_dtype, mu))
+        Y_ref = Y.copy()
+        fo.add_matrix_product_row_major(flat, op, alpha, X, beta, Y_ref, mu)
+        e.add_matrix_product_row_major(op, alpha, X, beta, Y, mu)
+        assert rel_err(Y, Y_ref) < TOL, op
+    e.close()
 
 
 @pytest.mark.parametrize("dtype", ["d", "z"])

@@ -128,8 +128,8 @@ def test_plan_statistics_and_overhead():
 
 MM_OPTION_SETS = [
     {},
-    dict(stage_bytes=8192, stage_z_bytes=1024, stage_z_elems=24, mm_stage_bytes=6144, mm_bin_cols=16, piece2_bytes=1024, bin_rows=20),
-    dict(stage_bytes=4096, stage_z_elems=12, mm_stage_bytes=4096, mm_bin_cols=5, piece2_bytes=512, bin_rows=9),
+    dict(mm_task_cols=40, mm1_kg=2, mm2_kg=3, bin_rows=20),   # split phase-1 units (partial T rows + reduce), short packets
+    dict(mm_task_cols=8, mm1_kg=1, mm2_kg=1, bin_rows=9),     # every leaf wider than 8 columns is split; one k-group per packet
 ]
 
 
@@ -150,14 +150,15 @@ def _check_mm(flat, op, opts, rng, mu):
 @pytest.mark.parametrize("name", helpers.golden_names())
 @pytest.mark.parametrize("oi", range(len(MM_OPTION_SETS)))
 def test_multi_rhs_streams_reproduce_oracle(name, oi):
-    """the multi-RHS plan (source-bin grouped phase 1, partial rows, operand rows of phase 2) on the golden H-matrices"""
+    """the multi-RHS plan (stacked V panels per source cluster with split units and partial rows, K-concatenated bin panels,
+    fragment-major packing, operand rows, K padding on zero rows) on the golden H-matrices"""
     flat, _ = load_golden(name)
     rng = np.random.default_rng(40 + oi)
     sym = flat.symmetry_for_leaves
     ops = ["N"] + (["T"] if sym != "H" else []) + (["C"] if flat.dtype == "z" and sym != "S" else [])
     for op in ops:
         st = _check_mm(flat, op, MM_OPTION_SETS[oi], rng, mu=3)
-    assert st["src_bins"] >= 1
+    assert st["units_mm1"] >= 1 and st["mm1_bytes"] > 0
 
 
 @pytest.mark.parametrize("seed", range(6))
@@ -168,37 +169,3 @@ def test_multi_rhs_synthetic_tilings(seed):
     flat = synthetic_flat(rng, m, n, dtype=dtype, max_leaf=int(rng.integers(4, 150)), max_rank=int(rng.integers(1, 150)))
     for opts in MM_OPTION_SETS:
         _check_mm(flat, "N", opts, rng, mu=int(rng.integers(1, 6)))
-
-
-def _check_mmf(flat, op, opts, rng, mu):
-    n_in, n_out = (flat.n_cols, flat.n_rows) if op == "N" else (flat.n_rows, flat.n_cols)
-    alpha, beta = (1.25, -0.75) if flat.dtype == "d" else (1.25 - 0.5j, 0.3 + 0.9j)
-    X = np.ascontiguousarray(helpers.rand_vec(rng, n_in, flat.np_dtype, mu))
-    Y0 = np.ascontiguousarray(helpers.rand_vec(rng, n_out, flat.np_dtype, mu))
-    Y_ref = Y0.copy()
-    fo.add_matrix_product_row_major(flat, op, alpha, X, beta, Y_ref, mu)
-    Y = Y0.copy()
-    helpers.emulate_mmf(flat, op, alpha, X, beta, Y, **opts)
-    assert rel_err(Y, Y_ref) < TOL
-
-
-@pytest.mark.parametrize("name", ["d_N_cylinder", "d_SL_cylinder", "z_N_sphere", "z_HL_cylinder"])
-@pytest.mark.parametrize("mu", [1, 5, 8, 13, 16, 24, 33, 40])
-def test_dfma_consumer_mapping_reproduces_oracle(name, mu):
-    """index arithmetic of the EXPERIMENTAL plain-DFMA multi-RHS consumer (csrc/kernels/mmf_kernels.cuh), emulated lane by lane
-    on the real packets: warp round-robin by piece_base, (group, row) lanes + group sums in phase 1, two bin rows per lane in
-    phase 2, chunked cross-warp sums, padded workspace rows with NaN pad columns, passes of 32 / 16 columns with column tails"""
-    flat, _ = load_golden(name)
-    rng = np.random.default_rng(mu)
-    for op in ["N"] + (["T"] if flat.symmetry_for_leaves != "H" else []):
-        _check_mmf(flat, op, MM_OPTION_SETS[0], rng, mu)
-
-
-@pytest.mark.parametrize("seed", range(4))
-def test_dfma_consumer_mapping_synthetic_tilings(seed):
-    rng = np.random.default_rng(700 + seed)
-    dtype = "dz"[seed % 2]
-    m, n = int(rng.integers(1, 300)), int(rng.integers(1, 300))
-    flat = synthetic_flat(rng, m, n, dtype=dtype, max_leaf=int(rng.integers(4, 150)), max_rank=int(rng.integers(1, 150)))
-    for opts in MM_OPTION_SETS:
-        _check_mmf(flat, "N", opts, rng, mu=int(rng.integers(1, 40)))
