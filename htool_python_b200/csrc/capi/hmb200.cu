@@ -613,9 +613,12 @@ void launch_mm(bool wide, int nt, unsigned grid, size_t smem, cudaStream_t st, c
         CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         kern<<<grid, kMmThreads, smem, st>>>(p);
     };
-    constexpr int MTW = PHASE == 1 ? 4 : 2, MTN = PHASE == 1 ? 2 : 1;   // m-tiles per warp: wide (4 x 2 warps) / narrow (8 x 1 warps)
-    constexpr int NTW = sizeof(T) == 8 ? 4 : 2;                         // n-tiles per warp of a wide pass (64 / 32 columns over 2 warp columns)
-    if (wide) go(hmatrix_mm_kernel<T, PHASE, 2, MTW, NTW>);
+    constexpr int MTN = PHASE == 1 ? 2 : 1;      // m-tiles per warp of a narrow pass (8 x 1 warps)
+    constexpr int NTW = sizeof(T) == 8 ? 4 : 2;  // n-tiles per warp of a wide pass over 2 warp columns (64 / 32 columns)
+    if (wide) {
+        if constexpr (PHASE == 1) go(hmatrix_mm_kernel<T, 1, 4, 8, NTW / 2>); // 2 x 4 warps, 8 m-tiles x (16 / 8 columns) each
+        else go(hmatrix_mm_kernel<T, 2, 2, 2, NTW>);                           // 4 x 2 warps, 2 m-tiles x (32 / 16 columns) each
+    }
     else if (nt <= 1) go(hmatrix_mm_kernel<T, PHASE, 1, MTN, 1>);
     else if (nt <= 2) go(hmatrix_mm_kernel<T, PHASE, 1, MTN, 2>);
     else if constexpr (sizeof(T) == 8) go(hmatrix_mm_kernel<T, PHASE, 1, MTN, 4>);

@@ -43,8 +43,9 @@ Options resolve_options(const hmb200_options *o) {
     r.piece1_bytes  = std::min(std::max(r.piece1_bytes, 256), piece_cap);
     r.piece2_bytes  = std::min(std::max(r.piece2_bytes, 256), piece_cap);
     r.unit_stages   = std::max(r.unit_stages, 1);
-    r.mm1_kg       = std::min(std::max(r.mm1_kg, 1), 6);   // 8 KiB per k-group of a 128-row panel
-    r.mm2_kg       = std::min(std::max(r.mm2_kg, 1), 12);  // 4 KiB per k-group of a 64-row panel
+    // even: the kernels' K loop alternates two fragment sets and runs on across packet boundaries (mm_kernels.cuh)
+    r.mm1_kg       = std::min(std::max(r.mm1_kg & ~1, 2), 6);   // 8 KiB per k-group of a 128-row panel
+    r.mm2_kg       = std::min(std::max(r.mm2_kg & ~1, 2), 12);  // 4 KiB per k-group of a 64-row panel
     r.mm_task_cols = std::max(r.mm_task_cols, 8);
     return r;
 }

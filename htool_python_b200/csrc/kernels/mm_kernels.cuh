@@ -16,8 +16,12 @@
 // one per run of operand rows (evict_last) into a ring of shared-memory stages guarded by full / empty mbarriers.  The eight
 // consumer warps tile the panel (WM x WN warps, MT m-tiles x NT n-tiles of 8 x 8 each) and keep C in DMMA accumulator registers
 // for the whole unit; A fragments come with one conflict-free 128-bit shared load per lane and k-group, B fragments from
-// operand rows at a padded stride (ld = 4 or 12 mod 16 doubles).  The next k-group's fragments are loaded before the DMMAs of
-// the current one are issued.  complex<double>: one complex DMMA step = 4 real DMMAs on the (re, im) parts.
+// operand rows at a padded stride (ld = 4 or 12 mod 16 doubles).  A unit is ONE software-pipelined K loop that runs across its
+// packets: the fragments of the next k-group -- also when it lives in the next packet (every packet but a unit's last holds an
+// even number of k-groups) -- are loaded before the DMMAs of the current one are issued, so the tensor pipe does not drain at
+// packet boundaries.  The hot loops carry no predicates (a runtime predicate in front of mma.sync costs a WARPSYNC + NOP per
+// instruction): the number of live m-tiles of a warp is a template parameter chosen once per unit.
+// complex<double>: one complex DMMA step = 4 real DMMAs on the (re, im) parts.
 #pragma once
 #include "../capi/plan.h"
 #include "ptx.cuh"
@@ -28,7 +32,8 @@ namespace hmb200 {
 
 constexpr int kMmConsumerWarps = 8;
 constexpr int kMmThreads       = (kMmConsumerWarps + 1) * 32;
-constexpr int kMmYTileBytes    = kMmRows2 * 72 * 8; // staged bin tile: 64 rows x (64 + 8 pad) doubles = 64 x (32 + 4) complex
+constexpr int kMmYTileRows     = 32;                      // the bin tile is staged in two halves of 32 rows
+constexpr int kMmYTileBytes    = kMmYTileRows * 72 * 8;   // 32 rows x (64 + 8 pad) doubles = 32 x (32 + 4) complex
 
 struct MmParams {
     const uint8_t *stream;
@@ -83,73 +88,334 @@ struct MmBFrag {
     T v[KS][NT];
 };
 
-// acc += panel chunk(s) of this packet x operand rows.  chunks: fragment-major (plan.h), 16 bytes per lane and (kg, mt);
-// Z: operand rows of the packet (stride ld).  The warp owns m-tiles wm, wm + WM, ... (nmt of them) and n-tiles c_base/8 ... (nnt).
-template <typename T, int MT, int NT>
-__device__ __forceinline__ void mm_packet(MmAcc<T, MT, NT> &acc, const double2 *chunks, int mt_panel, int n_kg, int wm, int WM, int nmt,
-                                          const T *Z, int ld, int c_base, int nnt, int lane) {
+// the consumer's view of the stage ring
+struct MmRing {
+    uint32_t bar_base;
+    uint8_t *stage_base;
+    uint32_t stage_sz;
+    int NS, slot;
+    uint32_t par;
+    __device__ __forceinline__ const uint8_t *wait() const { // current stage
+        ptx::mbar_wait(bar_base + 8u * slot, par);
+        return stage_base + (size_t)slot * stage_sz;
+    }
+    __device__ __forceinline__ const uint8_t *wait_next() const { // the stage after the current one, without leaving the current
+        const int ns = slot + 1 == NS ? 0 : slot + 1;
+        ptx::mbar_wait(bar_base + 8u * ns, ns == 0 ? par ^ 1u : par);
+        return stage_base + (size_t)ns * stage_sz;
+    }
+    __device__ __forceinline__ void release(int lane) { // all shared loads of the current stage have been issued by this warp
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(bar_base + 8u * (NS + slot));
+        if (++slot == NS) {
+            slot = 0;
+            par ^= 1u;
+        }
+    }
+};
+
+struct MmHeader {
+    int n_kg, rows, mt_panel;
+    uint32_t out0, flags, map_off16;
+    __device__ __forceinline__ explicit MmHeader(const uint8_t *pk) {
+        const uint4 h = *reinterpret_cast<const uint4 *>(pk);
+        n_kg = (int)h.x; out0 = h.y; rows = (int)(h.z & 0xffffu); mt_panel = (int)(h.z >> 16); flags = h.w & 0xffffu; map_off16 = h.w >> 16;
+    }
+};
+
+// One unit = one K loop over all its packets.  The warp owns m-tiles wm, wm + WM, ... (NMT live ones; with PRED the live counts
+// nmt <= NMT, nnt <= NT are runtime values and everything is predicated: only column tails and -- in the square tilings --
+// panels that end inside the warp's rows take that path).  TALL: a warp with many m-tiles and few n-tiles (wide pass of phase 1).
+// Returns with the unit's LAST packet still held (the caller reads the row map from it, then releases it).
+//   square tiling: A chunks ping-pong between two register sets; real: the B fragments of a k4-step are reloaded for the next
+//                  k-group right after their DMMAs were issued; complex: B ping-pongs too
+//   tall tiling  : B ping-pongs; an A chunk is reloaded for the next k-group right after the last DMMA that reads it; two sweeps
+//                  over the m-tiles per k-group keep DMMAs on one accumulator 2 x NMT x NT ... instructions apart
+template <typename T, int MT, int NT, int NMT, bool PRED, bool TALL>
+__device__ __forceinline__ const uint8_t *mm_unit(MmAcc<T, MT, NT> &acc, MmRing &ring, const uint8_t *pk, MmHeader &h, int stage_bytes, int ld, int wm, int WM,
+                                                  int c_base, int nnt, int nmt, int lane) {
     constexpr int KG = sizeof(T) == 8 ? 8 : 4;
     constexpr int KS = MmBFrag<T, NT>::KS;
     const int gid = lane >> 2, tig = lane & 3;
-    const double2 *ap = chunks + (size_t)wm * 32 + lane;
-    const int a_mt    = WM * 32, a_kg = mt_panel * 32;
-    const T *bp       = Z + (size_t)tig * ld + c_base + gid;
-    double2 a[MT];
-    MmBFrag<T, NT> b;
-    auto load = [&](double2 (&aa)[MT], MmBFrag<T, NT> &bb) {
+    const int a_mt = WM * 32, a_kg = h.mt_panel * 32;
+    const size_t b_kg = (size_t)KG * ld, b_k4 = (size_t)4 * ld;
+    const int a_off = wm * 32 + lane;
+    const size_t b_off = (size_t)tig * ld + c_base + gid;
+    const double2 *ap = reinterpret_cast<const double2 *>(pk + 16) + a_off;
+    const T *bp       = reinterpret_cast<const T *>(pk + stage_bytes) + b_off;
+    int n_kg = h.n_kg;
+    uint32_t flags = h.flags;
+    if (n_kg == 0) return pk; // a bin without coefficients: one empty packet
+
+    auto load_a = [&](double2 (&a)[NMT], const double2 *q) {
 #pragma unroll
-        for (int i = 0; i < MT; i++)
-            if (i < nmt) aa[i] = ap[i * a_mt];
+        for (int i = 0; i < NMT; i++)
+            if (!PRED || i < nmt) a[i] = q[i * a_mt];
+    };
+    auto load_b = [&](MmBFrag<T, NT> &b, const T *q) {
 #pragma unroll
         for (int ks = 0; ks < KS; ks++)
 #pragma unroll
             for (int j = 0; j < NT; j++)
-                if (j < nnt) bb.v[ks][j] = bp[(size_t)(4 * ks) * ld + 8 * j];
+                if (!PRED || j < nnt) b.v[ks][j] = q[(size_t)(4 * ks) * ld + 8 * j];
     };
-    load(a, b);
-    for (int kg = 0; kg < n_kg; kg++) {
-        double2 an[MT];
-        MmBFrag<T, NT> bn;
-        const bool more = kg + 1 < n_kg;
-        if (more) {
-            ap += a_kg;
-            bp += (size_t)KG * ld;
-            load(an, bn);
-        }
-        if constexpr (sizeof(T) == 8) {
+    auto load_bh = [&](T (&b)[NT], const T *q) { // one k4-step (real)
 #pragma unroll
-            for (int ks = 0; ks < 2; ks++)
+        for (int j = 0; j < NT; j++)
+            if (!PRED || j < nnt) b[j] = q[8 * j];
+    };
+    // the next packet of this unit: wait for it, leave the current one, re-base the fragment pointers
+    auto next_packet = [&]() {
+        const uint8_t *npk = ring.wait_next();
+        ring.release(lane);
+        pk = npk;
+        const uint4 hr = *reinterpret_cast<const uint4 *>(pk);
+        n_kg  = (int)hr.x;
+        flags = hr.w & 0xffffu;
+        ap    = reinterpret_cast<const double2 *>(pk + 16) + a_off;
+        bp    = reinterpret_cast<const T *>(pk + stage_bytes) + b_off;
+    };
+
+    if constexpr (TALL) {
+        double2 a[NMT];
+        MmBFrag<T, NT> b0, b1;
+        auto group = [&](const MmBFrag<T, NT> &b, bool reload, const double2 *anext) {
 #pragma unroll
-                for (int i = 0; i < MT; i++)
-                    if (i < nmt) {
-                        const double av = ks == 0 ? a[i].x : a[i].y;
+            for (int i = 0; i < NMT; i++)
 #pragma unroll
-                        for (int j = 0; j < NT; j++)
-                            if (j < nnt) dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], av, b.v[ks][j]);
+                for (int j = 0; j < NT; j++) {
+                    if (PRED && j >= nnt) continue;
+                    if constexpr (sizeof(T) == 8) {
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], a[i].x, b.v[0][j]);
+                    } else {
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], a[i].x, b.v[0][j].x);
+                        dmma884(acc.v[i][j][1][0], acc.v[i][j][1][1], a[i].x, b.v[0][j].y);
                     }
-        } else {
-#pragma unroll
-            for (int i = 0; i < MT; i++)
-                if (i < nmt) {
-#pragma unroll
-                    for (int j = 0; j < NT; j++)
-                        if (j < nnt) { // (ar + i ai)(br + i bi): re += ar br - ai bi ; im += ar bi + ai br
-                            dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], a[i].x, b.v[0][j].x);
-                            dmma884(acc.v[i][j][1][0], acc.v[i][j][1][1], a[i].x, b.v[0][j].y);
-                        }
-#pragma unroll
-                    for (int j = 0; j < NT; j++)
-                        if (j < nnt) {
-                            dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], -a[i].y, b.v[0][j].y);
-                            dmma884(acc.v[i][j][1][0], acc.v[i][j][1][1], a[i].y, b.v[0][j].x);
-                        }
                 }
-        }
-        if (more) {
 #pragma unroll
-            for (int i = 0; i < MT; i++) a[i] = an[i];
-            b = bn;
+            for (int i = 0; i < NMT; i++) {
+#pragma unroll
+                for (int j = 0; j < NT; j++) {
+                    if (PRED && j >= nnt) continue;
+                    if constexpr (sizeof(T) == 8) {
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], a[i].y, b.v[KS - 1][j]);
+                    } else {
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], -a[i].y, b.v[0][j].y);
+                        dmma884(acc.v[i][j][1][0], acc.v[i][j][1][1], a[i].y, b.v[0][j].x);
+                    }
+                }
+                if (reload) a[i] = anext[i * a_mt]; // the chunk of the next k-group, as soon as this one has been read
+            }
+        };
+        load_a(a, ap);
+        load_b(b0, bp);
+        for (;;) {
+            for (int kg = 0; kg < n_kg; kg += 2) {
+                const bool has1 = kg + 1 < n_kg;
+                if (has1) load_b(b1, bp + b_kg);
+                group(b0, has1, ap + a_kg);
+                if (has1) {
+                    if (kg + 2 < n_kg) {
+                        ap += 2 * a_kg;
+                        bp += 2 * b_kg;
+                        load_b(b0, bp);
+                        group(b1, true, ap);
+                    } else if (!(flags & kMmFlagLast)) { // the next k-group is the first of the next packet
+                        next_packet();
+                        load_b(b0, bp);
+                        group(b1, true, ap);
+                        kg = -2; // restart the k-group loop on the new packet
+                    } else {
+                        group(b1, false, ap);
+                    }
+                }
+            }
+            if (flags & kMmFlagLast) return pk;
+            // (only reached when a non-last packet held an odd number of k-groups, which the planner never emits)
+            next_packet();
+            load_a(a, ap);
+            load_b(b0, bp);
         }
+    } else if constexpr (sizeof(T) == 8) {
+        double2 a0[NMT], a1[NMT];
+        double b0[NT], b1[NT];
+        auto half = [&](const double2 (&a)[NMT], bool hi, const double (&b)[NT]) {
+#pragma unroll
+            for (int i = 0; i < NMT; i++) {
+                if (PRED && i >= nmt) continue;
+                const double av = hi ? a[i].y : a[i].x;
+#pragma unroll
+                for (int j = 0; j < NT; j++)
+                    if (!PRED || j < nnt) dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], av, b[j]);
+            }
+        };
+        load_a(a0, ap);
+        load_bh(b0, bp);
+        load_bh(b1, bp + b_k4);
+        for (;;) {
+            for (int kg = 0; kg < n_kg; kg += 2) {
+                const bool has1 = kg + 1 < n_kg;
+                if (has1) load_a(a1, ap + a_kg);
+                half(a0, false, b0);
+                if (has1) load_bh(b0, bp + b_kg);
+                half(a0, true, b1);
+                if (has1) {
+                    load_bh(b1, bp + b_kg + b_k4);
+                    const bool more = kg + 2 < n_kg, cross = !more && !(flags & kMmFlagLast);
+                    if (more) {
+                        ap += 2 * a_kg;
+                        bp += 2 * b_kg;
+                    } else if (cross) {
+                        next_packet();
+                        kg = -2;
+                    }
+                    if (more || cross) load_a(a0, ap);
+                    half(a1, false, b0);
+                    if (more || cross) load_bh(b0, bp);
+                    half(a1, true, b1);
+                    if (more || cross) load_bh(b1, bp + b_k4);
+                }
+            }
+            if (flags & kMmFlagLast) return pk;
+            next_packet();
+            load_a(a0, ap);
+            load_bh(b0, bp);
+            load_bh(b1, bp + b_k4);
+        }
+    } else {
+        double2 a0[NMT], a1[NMT];
+        MmBFrag<T, NT> b0, b1;
+        auto mma = [&](const double2 (&a)[NMT], const MmBFrag<T, NT> &b) {
+#pragma unroll
+            for (int i = 0; i < NMT; i++) {
+                if (PRED && i >= nmt) continue;
+#pragma unroll
+                for (int j = 0; j < NT; j++)
+                    if (!PRED || j < nnt) { // (ar + i ai)(br + i bi): re += ar br - ai bi ; im += ar bi + ai br
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], a[i].x, b.v[0][j].x);
+                        dmma884(acc.v[i][j][1][0], acc.v[i][j][1][1], a[i].x, b.v[0][j].y);
+                    }
+#pragma unroll
+                for (int j = 0; j < NT; j++)
+                    if (!PRED || j < nnt) {
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], -a[i].y, b.v[0][j].y);
+                        dmma884(acc.v[i][j][1][0], acc.v[i][j][1][1], a[i].y, b.v[0][j].x);
+                    }
+            }
+        };
+        load_a(a0, ap);
+        load_b(b0, bp);
+        for (;;) {
+            for (int kg = 0; kg < n_kg; kg += 2) {
+                const bool has1 = kg + 1 < n_kg;
+                if (has1) {
+                    load_a(a1, ap + a_kg);
+                    load_b(b1, bp + b_kg);
+                }
+                mma(a0, b0);
+                if (has1) {
+                    const bool more = kg + 2 < n_kg, cross = !more && !(flags & kMmFlagLast);
+                    if (more) {
+                        ap += 2 * a_kg;
+                        bp += 2 * b_kg;
+                    } else if (cross) {
+                        next_packet();
+                        kg = -2;
+                    }
+                    if (more || cross) {
+                        load_a(a0, ap);
+                        load_b(b0, bp);
+                    }
+                    mma(a1, b1);
+                }
+            }
+            if (flags & kMmFlagLast) return pk;
+            next_packet();
+            load_a(a0, ap);
+            load_b(b0, bp);
+        }
+    }
+}
+
+// column tail of a pass inside a tall warp tile (fewer live n-tiles than NT): plain predicated loop over the unit's packets, no
+// register double buffering (few registers; only the warps that straddle the last columns of a 33..63-column pass take it)
+template <typename T, int MT, int NT>
+__device__ __forceinline__ const uint8_t *mm_unit_plain(MmAcc<T, MT, NT> &acc, MmRing &ring, const uint8_t *pk, MmHeader &h, int stage_bytes, int ld, int wm, int WM,
+                                                        int c_base, int nnt, int nmt, int lane) {
+    constexpr int KG = sizeof(T) == 8 ? 8 : 4;
+    constexpr int KS = MmBFrag<T, NT>::KS;
+    const int gid = lane >> 2, tig = lane & 3;
+    int n_kg = h.n_kg;
+    uint32_t flags = h.flags;
+    for (;;) {
+        const double2 *ap = reinterpret_cast<const double2 *>(pk + 16) + wm * 32 + lane;
+        const T *bp       = reinterpret_cast<const T *>(pk + stage_bytes) + (size_t)tig * ld + c_base + gid;
+        for (int kg = 0; kg < n_kg; kg++, ap += h.mt_panel * 32, bp += (size_t)KG * ld) {
+            MmBFrag<T, NT> b;
+#pragma unroll
+            for (int ks = 0; ks < KS; ks++)
+#pragma unroll
+                for (int j = 0; j < NT; j++)
+                    if (j < nnt) b.v[ks][j] = bp[(size_t)(4 * ks) * ld + 8 * j];
+#pragma unroll
+            for (int i = 0; i < MT; i++) {
+                if (i >= nmt) continue;
+                const double2 a = ap[i * WM * 32];
+#pragma unroll
+                for (int j = 0; j < NT; j++) {
+                    if (j >= nnt) continue;
+                    if constexpr (sizeof(T) == 8) {
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], a.x, b.v[0][j]);
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], a.y, b.v[KS - 1][j]);
+                    } else {
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], a.x, b.v[0][j].x);
+                        dmma884(acc.v[i][j][1][0], acc.v[i][j][1][1], a.x, b.v[0][j].y);
+                        dmma884(acc.v[i][j][0][0], acc.v[i][j][0][1], -a.y, b.v[0][j].y);
+                        dmma884(acc.v[i][j][1][0], acc.v[i][j][1][1], a.y, b.v[0][j].x);
+                    }
+                }
+            }
+        }
+        if (flags & kMmFlagLast) return pk;
+        ring.release(lane);
+        pk = ring.wait();
+        const uint4 hr = *reinterpret_cast<const uint4 *>(pk);
+        n_kg  = (int)hr.x;
+        flags = hr.w & 0xffffu;
+    }
+}
+
+// a warp without live tiles in this unit (panel shorter than its rows, or a column tail) only walks the ring
+__device__ __forceinline__ const uint8_t *mm_skip_unit(MmRing &ring, const uint8_t *pk, uint32_t flags, int lane) {
+    while (!(flags & kMmFlagLast)) {
+        ring.release(lane);
+        pk    = ring.wait();
+        flags = reinterpret_cast<const uint4 *>(pk)->w & 0xffffu;
+    }
+    return pk;
+}
+
+template <typename T, int MT, int NT, int NMT, bool PRED>
+__device__ __forceinline__ const uint8_t *mm_tall_switch(MmAcc<T, MT, NT> &acc, MmRing &ring, const uint8_t *pk, MmHeader &h, int stage_bytes, int ld, int wm, int WM,
+                                                         int c_base, int nnt, int nmt, int lane) {
+    if (nmt == NMT) return mm_unit<T, MT, NT, NMT, PRED, true>(acc, ring, pk, h, stage_bytes, ld, wm, WM, c_base, nnt, NMT, lane);
+    if constexpr (NMT > 1) return mm_tall_switch<T, MT, NT, NMT - 1, PRED>(acc, ring, pk, h, stage_bytes, ld, wm, WM, c_base, nnt, nmt, lane);
+    else return pk;
+}
+
+template <typename T, int MT, int NT>
+__device__ __forceinline__ const uint8_t *mm_unit_dispatch(MmAcc<T, MT, NT> &acc, MmRing &ring, const uint8_t *pk, MmHeader &h, int stage_bytes, int ld, int wm, int WM,
+                                                           int c_base, int nnt, int nmt, int lane) {
+    if (nmt <= 0 || nnt <= 0) return mm_skip_unit(ring, pk, h.flags, lane);
+    if constexpr (MT >= 4) { // tall tiling: live m-tile count at compile time; a column tail predicates the n-tiles only
+        if (nnt == NT) return mm_tall_switch<T, MT, NT, MT, false>(acc, ring, pk, h, stage_bytes, ld, wm, WM, c_base, nnt, nmt, lane);
+        else return mm_unit_plain<T, MT, NT>(acc, ring, pk, h, stage_bytes, ld, wm, WM, c_base, nnt, nmt, lane);
+    } else {
+        if (nnt == NT && nmt == MT) return mm_unit<T, MT, NT, MT, false, false>(acc, ring, pk, h, stage_bytes, ld, wm, WM, c_base, nnt, nmt, lane);
+        if constexpr (MT == 2) {
+            if (nnt == NT && nmt == 1) return mm_unit<T, MT, NT, 1, false, false>(acc, ring, pk, h, stage_bytes, ld, wm, WM, c_base, nnt, nmt, lane);
+        }
+        return mm_unit<T, MT, NT, MT, true, false>(acc, ring, pk, h, stage_bytes, ld, wm, WM, c_base, nnt, nmt, lane);
     }
 }
 
@@ -160,8 +426,9 @@ __device__ __forceinline__ double mm_make<double>(double re, double) { return re
 template <>
 __device__ __forceinline__ double2 mm_make<double2>(double re, double im) { return make_double2(re, im); }
 
-// WN = 2: "wide" pass (4 x 2 warps, each MT x NT tiles); WN = 1: "narrow" pass (8 x 1 warps).  MT * 8 / WN m-tiles cover the
-// panel: 16 (128 rows) in phase 1, 8 (64 rows) in phase 2.
+// WM x WN = 8 consumer warps, each MT x NT tiles; WM * MT m-tiles cover the panel: 16 (128 rows) in phase 1, 8 (64 rows) in phase 2.
+// Wide passes: phase 2 runs 4 x 2 warps of 2 x 4 tiles, phase 1 runs 2 x 4 warps of 8 x 2 tiles (panels there have any number
+// of m-tiles: two warp rows with interleaved m-tiles balance to within one tile).  Narrow passes (<= 32 columns): 8 x 1 warps.
 template <typename T, int PHASE, int WN, int MT, int NT>
 __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParams p) {
     constexpr int NW = kMmConsumerWarps;
@@ -194,7 +461,8 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
         const uint64_t pol_stream = ptx::policy_evict_first(); // panel chunks are read exactly once
         const uint64_t pol_vec    = ptx::policy_evict_last();  // operand rows are shared by many units: keep them in L2
         const T *ws               = (const T *)p.ws;
-        uint32_t it = 0;
+        int slot = 0;
+        uint32_t par = 0;
         uint32_t u = 0;
         if (lane == 0) u = atomicAdd(p.counter, 1u);
         u = __shfl_sync(0xffffffffu, u, 0);
@@ -209,15 +477,13 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
                     me0 = __ldg(reinterpret_cast<const uint4 *>(p.stages + sb + lane));
                     me1 = __ldg(reinterpret_cast<const uint4 *>(p.stages + sb + lane) + 1);
                 }
-                for (uint32_t j = 0; j < cnt; j++, it++) {
+                for (uint32_t j = 0; j < cnt; j++) {
                     const uint32_t off_lo = __shfl_sync(0xffffffffu, me0.x, j), off_hi = __shfl_sync(0xffffffffu, me0.y, j);
                     const uint32_t bytes = __shfl_sync(0xffffffffu, me0.z, j), z_first = __shfl_sync(0xffffffffu, me0.w, j);
                     const uint32_t n_z = __shfl_sync(0xffffffffu, me1.x, j), z_bytes = __shfl_sync(0xffffffffu, me1.y, j);
                     const uint64_t gmem_off = (uint64_t)off_lo | ((uint64_t)off_hi << 32);
                     uint2 zc = make_uint2(0, 0);
                     if ((uint32_t)lane < n_z) zc = __ldg(reinterpret_cast<const uint2 *>(p.zcopies + z_first) + lane); // in flight during the wait
-                    const int slot       = it % NS;
-                    const uint32_t par   = (it / NS) & 1u;
                     const uint32_t sbase = ptx::smem_u32(stage_base + (size_t)slot * stage_sz);
                     ptx::mbar_wait(empty_bar(slot), par ^ 1u);
                     if (lane == 0) {
@@ -230,13 +496,15 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
                         const uint32_t zb = (zc.y & 0xffffu) * (uint32_t)ld, zdst = (zc.y >> 16) * (uint32_t)ld;
                         ptx::bulk_g2s(sbase + p.stage_bytes + zdst, ws + (size_t)zc.x * ld, zb, full_bar(slot), pol_vec);
                     }
+                    if (++slot == NS) {
+                        slot = 0;
+                        par ^= 1u;
+                    }
                 }
             }
             u = __shfl_sync(0xffffffffu, u_next, 0);
         }
         { // terminate packet: a header written through the generic proxy, released by a plain arrive
-            const int slot     = it % NS;
-            const uint32_t par = (it / NS) & 1u;
             ptx::mbar_wait(empty_bar(slot), par ^ 1u);
             if (lane == 0) {
                 *reinterpret_cast<uint4 *>(stage_base + (size_t)slot * stage_sz) = make_uint4(0u, 0u, 0u, kMmFlagTerminate);
@@ -254,30 +522,23 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
     const int nnt    = max(0, min(NT, (ncols8 - c_base) >> 3)); // n-tiles of this warp that hold right-hand sides
     MmAcc<T, MT, NT> acc;
     acc.clear();
+    MmRing ring{bar_base, stage_base, stage_sz, NS, 0, 0u};
     T *ws = (T *)p.ws;
-    for (uint32_t it = 0;; it++) {
-        const int slot     = it % NS;
-        const uint32_t par = (it / NS) & 1u;
-        ptx::mbar_wait(full_bar(slot), par);
-        const uint8_t *pk   = stage_base + (size_t)slot * stage_sz;
-        const uint4 hraw    = *reinterpret_cast<const uint4 *>(pk);
-        const int n_kg      = (int)hraw.x;
-        const uint32_t out0 = hraw.y;
-        const int rows = (int)(hraw.z & 0xffffu), mt_panel = (int)(hraw.z >> 16);
-        const uint32_t flags = hraw.w & 0xffffu, map_off16 = hraw.w >> 16;
-        if (flags & kMmFlagTerminate) break;
-        const int nmt = wm < mt_panel ? min(MT, (mt_panel - wm + WM - 1) / WM) : 0; // m-tiles wm, wm + WM, ... below mt_panel
-
-        if (nmt > 0 && nnt > 0 && n_kg > 0)
-            mm_packet<T, MT, NT>(acc, reinterpret_cast<const double2 *>(pk + 16), mt_panel, n_kg, wm, WM, nmt, reinterpret_cast<const T *>(pk + p.stage_bytes), ld, c_base, nnt, lane);
+    for (;;) {
+        const uint8_t *pk = ring.wait();
+        MmHeader h(pk);
+        if (h.flags & kMmFlagTerminate) break;
+        const int nmt = wm < h.mt_panel ? min(MT, (h.mt_panel - wm + WM - 1) / WM) : 0; // m-tiles wm, wm + WM, ... below mt_panel
+        const bool live = nmt > 0 && nnt > 0;
+        const uint8_t *lpk = mm_unit_dispatch<T, MT, NT>(acc, ring, pk, h, p.stage_bytes, ld, wm, WM, c_base, nnt, nmt, lane);
 
         if (PHASE == 1) {
-            if (flags & kMmFlagLast) { // the unit's rows of T (or partial rows): destination row per panel row from the packet's row map
-                const uint32_t *map = reinterpret_cast<const uint32_t *>(pk + 16 * (size_t)map_off16);
+            if (live) { // the unit's rows of T (or partial rows): destination row per panel row from the last packet's row map
+                const uint32_t *map = reinterpret_cast<const uint32_t *>(lpk + 16 * (size_t)(reinterpret_cast<const uint4 *>(lpk)->w >> 16));
 #pragma unroll
                 for (int i = 0; i < MT; i++) {
                     const int r = 8 * (wm + WM * i) + gid;
-                    if (i < nmt && r < rows) {
+                    if (i < nmt && r < h.rows) {
                         T *orow = ws + (size_t)map[r] * ld;
 #pragma unroll
                         for (int j = 0; j < NT; j++)
@@ -294,20 +555,21 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
                 }
                 acc.clear();
             }
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(empty_bar(slot));
+            ring.release(lane);
         } else {
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(empty_bar(slot));
-            if (flags & kMmFlagLast) {
-                // stage the bin's tile in shared memory, then all consumer threads store full rows: the local Y (with beta) and
-                // the same bits into every peer's replicated block (fused all-gather)
-                constexpr int ldt = kMmYTileBytes / kMmRows2 / (int)sizeof(T);
-                T *yt = reinterpret_cast<T *>(ytile_raw);
+            ring.release(lane);
+            // stage the bin's tile in shared memory (two halves of 32 rows), then all consumer threads store full rows: the local
+            // Y (with beta) and the same bits into every peer's replicated block (fused all-gather)
+            constexpr int ldt = kMmYTileBytes / kMmYTileRows / (int)sizeof(T);
+            T *yt = reinterpret_cast<T *>(ytile_raw);
+            const T alpha = mm_make<T>(p.alpha_re, p.alpha_im), beta = mm_make<T>(p.beta_re, p.beta_im);
+            const bool beta_zero = Scalar<T>::is_zero(beta);
+            for (int hf = 0; hf * kMmYTileRows < h.rows; hf++) {
 #pragma unroll
                 for (int i = 0; i < MT; i++) {
-                    const int r = 8 * (wm + WM * i) + gid;
-                    if (i < nmt) {
+                    const int mt = wm + WM * i;
+                    if (live && i < nmt && (mt >> 2) == hf) {
+                        const int r = 8 * (mt & 3) + gid;
 #pragma unroll
                         for (int j = 0; j < NT; j++)
                             if (j < nnt) {
@@ -322,14 +584,13 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
                     }
                 }
                 ptx::named_bar_sync(1, NW * 32);
-                const T alpha = mm_make<T>(p.alpha_re, p.alpha_im), beta = mm_make<T>(p.beta_re, p.beta_im);
-                const bool beta_zero = Scalar<T>::is_zero(beta);
-                const uint32_t nc = (uint32_t)p.ncols, per_tgt = (uint32_t)rows * nc, total = (uint32_t)(1 + p.n_peers) * per_tgt;
+                const uint32_t rows_h = (uint32_t)min(kMmYTileRows, h.rows - hf * kMmYTileRows);
+                const uint32_t nc = (uint32_t)p.ncols, per_tgt = rows_h * nc, total = (uint32_t)(1 + p.n_peers) * per_tgt;
                 for (uint32_t idx = threadIdx.x; idx < total; idx += (uint32_t)NW * 32u) {
                     const uint32_t tgt = idx / per_tgt, rem = idx - tgt * per_tgt;
                     const uint32_t r = rem / nc, c = rem - r * nc;
-                    T v = Scalar<T>::mul(alpha, yt[r * ldt + c]); // rows above mt_panel * 8 are never read: r < rows
-                    const size_t o = (size_t)(out0 + r) * p.ldy + c;
+                    T v = Scalar<T>::mul(alpha, yt[r * ldt + c]);
+                    const size_t o = (size_t)(h.out0 + hf * kMmYTileRows + r) * p.ldy + c;
                     if (tgt == 0) {
                         T *y = (T *)p.y;
                         if (!beta_zero) v = Scalar<T>::add(v, Scalar<T>::mul(beta, y[o])); // beta == 0 must not propagate NaNs of y (BLAS)
@@ -338,9 +599,9 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
                         reinterpret_cast<T *>(p.peer_y[tgt - 1])[o] = v; // beta = 0 on the fused path
                     }
                 }
-                ptx::named_bar_sync(1, NW * 32); // the tile is rewritten by the next bin
-                acc.clear();
+                ptx::named_bar_sync(1, NW * 32); // the tile is rewritten by the next half / the next bin
             }
+            acc.clear();
         }
     }
     if (PHASE == 2 && p.n_flags > 0) {

@@ -482,7 +482,7 @@ def test_multi_rhs_dmma(name, mu):
 
 
 @pytest.mark.parametrize("name,mu", [("d_N_cylinder", 64), ("d_N_rect", 9), ("z_N_sphere", 32), ("z_HL_cylinder", 6)])
-@pytest.mark.parametrize("opts", [dict(mm_task_cols=40, mm1_kg=2, mm2_kg=3, bin_rows=20), dict(mm_task_cols=8, mm1_kg=1, mm2_kg=1, bin_rows=9), dict(mm1_kg=6, mm2_kg=12)])
+@pytest.mark.parametrize("opts", [dict(mm_task_cols=40, mm1_kg=2, mm2_kg=4, bin_rows=20), dict(mm_task_cols=8, mm1_kg=2, mm2_kg=2, bin_rows=9), dict(mm1_kg=6, mm2_kg=10)])
 def test_multi_rhs_dmma_split_units(name, mu, opts):
     """the multi-RHS kernels on schedules with split phase-1 units (partial T rows + reduce_rows_kernel), short and long packets,
     small bins (panels with few m-tiles) vs the oracle"""

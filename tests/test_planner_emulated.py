@@ -128,8 +128,8 @@ def test_plan_statistics_and_overhead():
 
 MM_OPTION_SETS = [
     {},
-    dict(mm_task_cols=40, mm1_kg=2, mm2_kg=3, bin_rows=20),   # split phase-1 units (partial T rows + reduce), short packets
-    dict(mm_task_cols=8, mm1_kg=1, mm2_kg=1, bin_rows=9),     # every leaf wider than 8 columns is split; one k-group per packet
+    dict(mm_task_cols=40, mm1_kg=2, mm2_kg=4, bin_rows=20),   # split phase-1 units (partial T rows + reduce), short packets
+    dict(mm_task_cols=8, mm1_kg=2, mm2_kg=2, bin_rows=9),     # every leaf wider than 8 columns is split; two k-groups per packet
 ]
 
 
