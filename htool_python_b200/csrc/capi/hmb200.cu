@@ -119,6 +119,8 @@ struct hmb200_handle {
     size_t pinned_bytes = 0;
     uint32_t *counters = nullptr; // [2]
     int32_t *perm_t = nullptr, *perm_s = nullptr;
+    int32_t *gperm_s = nullptr, *ginv_t = nullptr; // distributed user-numbering product: full source permutation, inverse target permutation
+    void *gx = nullptr, *gy = nullptr;             // ... and its chunk staging (n_global elements each, never reallocated: cached graphs hold them)
     // per-kernel timing: a ring of CUDA-event quads recorded on the launching stream, collected lazily (no sync in the
     // product path); kTimingSlots products are remembered
     static constexpr int kTimingSlots = 256;
@@ -917,6 +919,64 @@ int fused_mm_product(hmb200_handle *h, const double *alpha, const void *in, int 
     return 0;
 }
 
+// y_user[r0 : r0 + rcnt] of y = A x on every rank, from this rank's chunk x_user[c0 : c0 + cnt] of the replicated input, as ONE
+// cached CUDA graph: H2D of the chunk, all-gather of the chunks over the peer regions, global_to_root_cluster, the slab product
+// with the fused all-gather of its rows, root_cluster_to_global of the rank's chunk of the result, D2H.  The distributed
+// global-to-global product (add_distributed_operator_vector_product_global_to_global.hpp:96-118) with n / P elements per rank and
+// direction over PCIe.  Host pointers must be page-locked; synchronous on return.
+template <typename T>
+int user_matvec_chunked(hmb200_handle *h, const void *x_host, int64_t c0, int64_t cnt, void *y_host, int64_t r0, int64_t rcnt) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    hmb200_handle::Peer &pr = h->peer;
+    if (!pr.attached) throw std::runtime_error("hmb200_peer_attach has not been called");
+    if (!h->gperm_s || !h->ginv_t) throw std::runtime_error("hmb200_set_global_permutations has not been called");
+    PackedOp &po = h->ops[0];
+    if ((int64_t)po.n_in != pr.n_global) throw std::runtime_error("the chunked user-numbering product needs a square operator");
+    if (c0 < 0 || cnt < 0 || c0 + cnt > pr.n_global || r0 < 0 || rcnt < 0 || r0 + rcnt > pr.n_global) throw std::runtime_error("chunk outside the vector");
+    if ((cnt && !host_is_pinned(x_host)) || (rcnt && !host_is_pinned(y_host))) throw std::runtime_error("the host chunks must be page-locked (cudaHostAlloc / cudaHostRegister)");
+    const int buf_x = (int)(pr.products & 1);
+    pr.products++;
+    const int buf_y = (int)(pr.products & 1);
+    pr.products++;
+    hmb200_handle::GraphKey key;
+    std::memset(&key, 0, sizeof(key));
+    key.op = 'U'; key.in = x_host; key.out = y_host; key.fused = 16 + buf_x;
+    key.a[0] = (double)c0; key.a[1] = (double)cnt; key.b[0] = (double)r0; key.b[1] = (double)rcnt;
+    const double one[2] = {1.0, 0.0}, zero[2] = {0.0, 0.0};
+    run_cached(h, key, [&] {
+        if (cnt) CUDA_CHECK(cudaMemcpyAsync(h->gx, x_host, (size_t)cnt * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+        {   // all-gather of the user-numbered chunks into buffer buf_x of every rank
+            PeerGatherParams p{};
+            p.src = h->gx; p.n_local = cnt; p.n_targets = pr.n_ranks;
+            for (int q = 0; q < pr.n_ranks; q++) {
+                p.dst[q]   = pr.region[q] + (size_t)buf_x * pr.buf_bytes + (size_t)c0 * sizeof(T);
+                p.flags[q] = peer_ctrl_flags(pr, q, buf_x) + pr.rank;
+            }
+            p.epoch = peer_ctrl_epoch(pr, buf_x);
+            p.done  = peer_ctrl_done(pr);
+            const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>((cnt + 2047) / 2048, 64));
+            peer_gather_kernel<T><<<grid, 256, 0, h->stream>>>(p);
+            peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf_x), pr.n_ranks, peer_ctrl_epoch(pr, buf_x), peer_ctrl_err(pr), pr.wait_cycles);
+        }
+        const int tb = 256;
+        const T *xu = reinterpret_cast<const T *>(pr.region[pr.rank] + (size_t)buf_x * pr.buf_bytes);
+        permute_gather_kernel<T><<<(unsigned)std::min<size_t>(((size_t)po.n_in + tb - 1) / tb + 1, 4096), tb, 0, h->stream>>>(h->gperm_s, 0, po.n_in, xu, (T *)h->xz, 1);
+        uint8_t *yb = pr.region[pr.rank] + (size_t)buf_y * pr.buf_bytes;
+        run_product<T>(h, po, one, zero, yb + (size_t)pr.slab_offset * sizeof(T), nullptr, buf_y);
+        peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf_y), pr.n_ranks, peer_ctrl_epoch(pr, buf_y), peer_ctrl_err(pr), pr.wait_cycles);
+        if (rcnt) {
+            permute_gather_kernel<T><<<(unsigned)std::min<size_t>(((size_t)rcnt + tb - 1) / tb + 1, 4096), tb, 0, h->stream>>>(h->ginv_t + r0, 0, (int)rcnt, (const T *)yb, (T *)h->gy, 1);
+            CUDA_CHECK(cudaMemcpyAsync(y_host, h->gy, (size_t)rcnt * sizeof(T), cudaMemcpyDeviceToHost, h->stream));
+        }
+        h->launches += 5;
+        CUDA_CHECK(cudaGetLastError());
+    });
+    CUDA_CHECK(cudaStreamSynchronize(h->stream));
+    const int err = *(volatile int *)pr.err_host;
+    if (err) throw std::runtime_error("a peer did not arrive within the wait bound (status " + std::to_string(err) + ")");
+    return 0;
+}
+
 template <typename F>
 int guarded(F &&f) {
     try {
@@ -976,6 +1036,10 @@ void hmb200_destroy(hmb200_handle *h) {
     cudaFree(h->counters);
     cudaFree(h->perm_t);
     cudaFree(h->perm_s);
+    cudaFree(h->gperm_s);
+    cudaFree(h->ginv_t);
+    cudaFree(h->gx);
+    cudaFree(h->gy);
     if (h->pinned) cudaFreeHost(h->pinned);
     for (auto &ev : h->ev)
         if (ev) cudaEventDestroy(ev);
@@ -1113,6 +1177,27 @@ int hmb200_matrix_product_allgather_d(hmb200_handle *h, const double *alpha, con
 }
 int hmb200_matrix_product_allgather_z(hmb200_handle *h, const double *alpha, const double *in, int mu, void **y_replicated) {
     return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return fused_mm_product<double2>(h, alpha, in, mu, y_replicated); });
+}
+int hmb200_set_global_permutations(hmb200_handle *h, const int32_t *source_perm, int64_t n_source, const int32_t *inverse_target_perm, int64_t n_target) {
+    return guarded([&] {
+        if (!h || !source_perm || !inverse_target_perm) throw std::runtime_error("null argument");
+        if (n_source != h->n_cols || n_target < h->n_rows) throw std::runtime_error("permutation sizes do not match the operator");
+        CUDA_CHECK(cudaSetDevice(h->device));
+        if (!h->gperm_s) CUDA_CHECK(cudaMalloc(&h->gperm_s, sizeof(int32_t) * (size_t)std::max<int64_t>(n_source, 1)));
+        if (!h->ginv_t) CUDA_CHECK(cudaMalloc(&h->ginv_t, sizeof(int32_t) * (size_t)std::max<int64_t>(n_target, 1)));
+        if (!h->gx) CUDA_CHECK(cudaMalloc(&h->gx, (size_t)std::max<int64_t>(n_source, 1) * h->es));
+        if (!h->gy) CUDA_CHECK(cudaMalloc(&h->gy, (size_t)std::max<int64_t>(n_target, 1) * h->es));
+        CUDA_CHECK(cudaMemcpyAsync(h->gperm_s, source_perm, sizeof(int32_t) * (size_t)n_source, cudaMemcpyHostToDevice, h->stream));
+        CUDA_CHECK(cudaMemcpyAsync(h->ginv_t, inverse_target_perm, sizeof(int32_t) * (size_t)n_target, cudaMemcpyHostToDevice, h->stream));
+        CUDA_CHECK(cudaStreamSynchronize(h->stream));
+        return 0;
+    });
+}
+int hmb200_matvec_user_chunked_d(hmb200_handle *h, const double *x_chunk, int64_t c0, int64_t count, double *y_chunk, int64_t r0, int64_t rcount) {
+    return guarded([&] { if (!h || h->es != 8) throw std::runtime_error("handle is not a real (double) engine"); return user_matvec_chunked<double>(h, x_chunk, c0, count, y_chunk, r0, rcount); });
+}
+int hmb200_matvec_user_chunked_z(hmb200_handle *h, const double *x_chunk, int64_t c0, int64_t count, double *y_chunk, int64_t r0, int64_t rcount) {
+    return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return user_matvec_chunked<double2>(h, x_chunk, c0, count, y_chunk, r0, rcount); });
 }
 int hmb200_peer_buffer(hmb200_handle *h, int index, void **ptr) {
     if (!h || !ptr || index < 0 || index > 1 || !h->peer.region[h->peer.rank]) { g_last_error = "no peer region / bad index"; return 1; }

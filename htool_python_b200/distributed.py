@@ -256,6 +256,11 @@ class B200DistributedOperator:
         inv[self.perm_t.long()] = torch.arange(self.n_target, dtype=torch.int32, device=self.device)
         self._inv_perm_t = inv  # y_user[i] = y_cluster[inv[i]]
         self.shared_result_timeout_s = 120.0
+        # the whole chunked product as one call / one cached CUDA graph (hmb200_matvec_user_chunked_*)
+        ps = np.ascontiguousarray(self.perm_s.cpu().numpy(), np.int32)
+        it = np.ascontiguousarray(inv.cpu().numpy(), np.int32)
+        _lib.check(_lib.lib().hmb200_set_global_permutations(self.engine._h, ps.ctypes.data, len(ps), it.ctypes.data, len(it)))
+        self._pin_x_chunk = torch.empty(self.n_source, dtype=self.torch_dtype).pin_memory()
 
     @property
     def shape(self):
@@ -508,6 +513,8 @@ class B200DistributedOperator:
             bad = out is not None and (not isinstance(out, np.ndarray) or out.dtype != self.np_dtype or out.shape != (self.n_target,) or not out.flags.c_contiguous)
         if bad:
             raise ValueError("out must be a contiguous numpy array of the operator's dtype and target size, or the string 'shared'")
+        if self.fused and self.world > 1 and getattr(self, "_shm", None) is not None and self.split_input_upload:
+            return self._matvec_chunked(x, out)
         (xu, xc, yc, yu), (pin_x, pin_y) = self._buffers(1)
         with torch.cuda.device(self.device):
             src = self._as_pinned_tensor(x)
@@ -538,6 +545,41 @@ class B200DistributedOperator:
             return pin_y.numpy().copy() if out is None else pin_y.numpy()
         if dst is None:
             out[:] = pin_y.numpy()
+        return out
+
+    def _matvec_chunked(self, x, out):
+        """the distributed user-numbering product as ONE library call per rank (one cached CUDA graph: H2D of this rank's 1/P
+        chunk of x, all-gather of the chunks over NVLink, permutation, slab product with the fused all-gather, permutation of this
+        rank's 1/P chunk of y, D2H into the node-shared page-locked result vector), then the host-side flags."""
+        import time
+
+        k = self._shm_calls
+        self._shm_calls += 1
+        b = k & 1
+        n, es = self.n_source, self.es
+        c0, c1 = self.rank * n // self.world, (self.rank + 1) * n // self.world
+        src = self._as_pinned_tensor(x)
+        if src is None:  # pageable input: stage this rank's chunk
+            self._pin_x_chunk.numpy()[c0:c1] = x[c0:c1].astype(self.np_dtype, copy=False)
+            src = self._pin_x_chunk
+        res = self._shm_y[b]
+        fn = _lib.lib().hmb200_matvec_user_chunked_z if self.is_complex else _lib.lib().hmb200_matvec_user_chunked_d
+        self.engine.set_stream(__import__("torch").cuda.current_stream(self.device).cuda_stream)
+        st = fn(self.engine._h, src.data_ptr() + es * c0, c0, c1 - c0, res.ctypes.data + es * c0, c0, c1 - c0)
+        if st != 0:
+            self._peer_failed = self._peer_failed or self.peer_status(sync=False) or 1
+            _lib.check(st)
+        fl = self._shm_flags
+        fl[self.rank] = k + 1
+        t0 = time.perf_counter()
+        while int(fl.min()) < k + 1:
+            if time.perf_counter() - t0 > self.shared_result_timeout_s:
+                raise RuntimeError(f"hmb200: rank {int(fl.argmin())} did not deliver its chunk of the result within {self.shared_result_timeout_s} s")
+        if isinstance(out, str):
+            return res
+        if out is None:
+            return res.copy()
+        np.copyto(out, res)
         return out
 
     def _finish_shared(self, yc, yu, out):

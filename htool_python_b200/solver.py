@@ -145,6 +145,8 @@ def gmres_driver(sp, b_host, x_host, opt: dict):
                     n2_dev = sp.combine(V, k, 1, hk, -1.0, w, want_norm=(k == i))
                     hs.append(hk)
                 token = sp.host_begin(hs + [n2_dev])
+            elif hasattr(sp, "cgs_step"):  # the same two kernels + two reductions on preallocated buffers, one read-back
+                h_dev, n2_dev, token = sp.cgs_step(V, i + 1, w)
             else:  # classical Gram-Schmidt (:541-552)
                 h_dev = sp.dots(V, 0, i + 1, w)
                 n2_dev = sp.combine(V, 0, i + 1, h_dev, -1.0, w, want_norm=True)
@@ -480,6 +482,30 @@ class CudaKrylovSpace:
             dist.all_reduce(self.torch.view_as_real(t) if t.is_complex() else t, group=self.group)
         return t
 
+    def cgs_step(self, V, k, w):
+        """one classical Gram-Schmidt step against the first k basis vectors (HPDDM_iterative.hpp:541-552): h = V^H w, all-reduce,
+        w -= V h with ||w||^2, all-reduce, and the asynchronous read-back of [h | ||w||^2] -- h and the norm live next to each
+        other in one preallocated device buffer, so the step allocates nothing and reads back with one copy."""
+        torch = self.torch
+        c = 2 if self.dtype == torch.complex128 else 1
+        if getattr(self, "_hbuf", None) is None or self._hbuf.numel() < c * k + 1:
+            self._hbuf = torch.empty(max(c * (k + 64) + 1, 256), dtype=torch.float64, device=self.device)
+            self._hpin2 = torch.empty(self._hbuf.numel(), dtype=torch.float64).pin_memory()
+            self._hev = self._hev or torch.cuda.Event()
+        hb = self._hbuf
+        h = torch.view_as_complex(hb[:2 * k].view(k, 2)) if c == 2 else hb[:k]
+        n2 = hb[c * k:c * k + 1]
+        self._reserve(k)
+        st = self._stream()
+        _lib.check(self.lib.hmb200_krylov_dots(V.row(0).data_ptr(), V.n, k, w.data_ptr(), self.n_local, h.data_ptr(), self._scratch.data_ptr(), self.es, st))
+        self._allreduce(h)
+        _lib.check(self.lib.hmb200_krylov_combine(V.row(0).data_ptr(), V.n, k, h.data_ptr(), -1.0, w.data_ptr(), self.n_local, n2.data_ptr(), self._scratch.data_ptr(), self.es, st))
+        self._allreduce(n2)
+        self.kernel_launches += 4
+        self._hpin2[:c * k + 1].copy_(hb[:c * k + 1], non_blocking=True)
+        self._hev.record(torch.cuda.current_stream(self.device))
+        return h, n2, ("flat", c == 2, k)
+
     def dots(self, V, first, k, w, reduce=True):
         h = self.torch.empty(k, dtype=self.dtype, device=self.device)
         self._reserve(k)
@@ -544,6 +570,12 @@ class CudaKrylovSpace:
     def host_end(self, token):
         self._hev.synchronize()
         self._check_peers()
+        if isinstance(token, tuple) and token and token[0] == "flat":  # cgs_step: [h (k values) | ||w||^2]
+            _, is_c, k = token
+            vals = self._hpin2.numpy()
+            if is_c:
+                return [vals[:2 * k].view(np.complex128).copy(), vals[2 * k:2 * k + 1].copy()]
+            return [vals[:k].copy(), vals[k:k + 1].copy()]
         vals = self._hpin.numpy()
         out, p = [], 0
         for is_c, n in token:

@@ -159,6 +159,19 @@ int hmb200_peer_mm_attach(hmb200_handle *h, const unsigned char *ipc_handles);
 int hmb200_peer_mm_buffer(hmb200_handle *h, int index, void **ptr);
 int hmb200_matrix_product_allgather_d(hmb200_handle *h, const double *alpha, const double *in, int mu, void **y_replicated);
 int hmb200_matrix_product_allgather_z(hmb200_handle *h, const double *alpha, const double *in, int mu, void **y_replicated);
+/* y = A x in USER numbering across the ranks of one node with n / P elements per rank and direction over PCIe (the replicated-input
+ * / replicated-result contract of the reference's DistributedOperator.__mul__, src/htool/distributed_operator/distributed_operator.hpp:23-37,
+ * add_distributed_operator_vector_product_global_to_global.hpp:96-118).  After hmb200_peer_attach and
+ * hmb200_set_global_permutations(h, source permutation (n_cols, cluster slot -> user index), its size, INVERSE target permutation
+ * (user index -> cluster slot, n_global), its size), collectively:
+ *   hmb200_matvec_user_chunked_{d,z}(h, x_chunk, c0, count, y_chunk, r0, rcount)
+ * uploads this rank's chunk x_user[c0 : c0+count] (page-locked host pointer), all-gathers the chunks over the peer regions,
+ * permutes, multiplies (fused all-gather of the rows), and downloads y_user[r0 : r0+rcount] into y_chunk (page-locked host
+ * pointer, e.g. this rank's window of one node-shared vector).  One cached CUDA graph; synchronous on return; counts as two
+ * collectives of the sequence above. */
+int hmb200_set_global_permutations(hmb200_handle *h, const int32_t *source_perm, int64_t n_source, const int32_t *inverse_target_perm, int64_t n_target);
+int hmb200_matvec_user_chunked_d(hmb200_handle *h, const double *x_chunk, int64_t c0, int64_t count, double *y_chunk, int64_t r0, int64_t rcount);
+int hmb200_matvec_user_chunked_z(hmb200_handle *h, const double *x_chunk, int64_t c0, int64_t count, double *y_chunk, int64_t r0, int64_t rcount);
 /* the solver's two collectives on the same peer regions (no NCCL / MPI on the iteration path):
  *   hmb200_peer_allgather     local slab (n_rows elements, device) -> replicated vector on every rank
  *                             (MPI_Allgatherv of ..._vector_product_local_to_local.hpp:44); counts as one collective of step 3
