@@ -609,22 +609,34 @@ int vector_product(hmb200_handle *h, char trans, const double *alpha, const void
 }
 
 // ---- multi-RHS on the DMMA panel kernels (kernels/mm_kernels.cuh) --------------------------------------------------------------
+// warp tiling by the number of n-tiles (8 columns each) of the pass; the eight consumer warps form WM x WN, each MT x NT tiles:
+//   n-tiles   phase 1 (16 m-tiles)          phase 2 (8 m-tiles)
+//   1         8 x 1 warps, 2 x 1 tiles      8 x 1 warps, 1 x 1 tiles
+//   2         8 x 1 warps, 2 x 2 tiles      8 x 1 warps, 1 x 2 tiles        (measured faster than 4 x 2 warps at 16 columns)
+//   3, 4      4 x 2 warps, 4 x 2 tiles      4 x 2 warps, 2 x 2 tiles
+//   5 .. 8    2 x 4 warps, 8 x 2 tiles      4 x 2 warps, 2 x 4 tiles        (real only; complex passes hold <= 4 n-tiles)
+// complex, 3-4 n-tiles, phase 1: 2 x 4 warps, 8 x 1 tiles
 template <typename T, int PHASE>
-void launch_mm(bool wide, int nt, unsigned grid, size_t smem, cudaStream_t st, const MmParams &p) {
+void launch_mm(int nt, unsigned grid, size_t smem, cudaStream_t st, const MmParams &p) {
     auto go = [&](auto kern) {
         CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         kern<<<grid, kMmThreads, smem, st>>>(p);
     };
-    constexpr int MTN = PHASE == 1 ? 2 : 1;      // m-tiles per warp of a narrow pass (8 x 1 warps)
-    constexpr int NTW = sizeof(T) == 8 ? 4 : 2;  // n-tiles per warp of a wide pass over 2 warp columns (64 / 32 columns)
-    if (wide) {
-        if constexpr (PHASE == 1) go(hmatrix_mm_kernel<T, 1, 4, 8, NTW / 2>); // 2 x 4 warps, 8 m-tiles x (16 / 8 columns) each
-        else go(hmatrix_mm_kernel<T, 2, 2, 2, NTW>);                           // 4 x 2 warps, 2 m-tiles x (32 / 16 columns) each
+    if constexpr (PHASE == 1) {
+        if (nt <= 1) go(hmatrix_mm_kernel<T, 1, 1, 2, 1>);
+        else if (nt == 2) go(hmatrix_mm_kernel<T, 1, 1, 2, 2>);
+        else if (nt <= 4) {
+            if constexpr (sizeof(T) == 8) go(hmatrix_mm_kernel<T, 1, 2, 4, 2>);
+            else go(hmatrix_mm_kernel<T, 1, 4, 8, 1>);
+        } else if constexpr (sizeof(T) == 8) go(hmatrix_mm_kernel<T, 1, 4, 8, 2>);
+        else throw std::runtime_error("internal: complex passes hold at most 32 columns");
+    } else {
+        if (nt <= 1) go(hmatrix_mm_kernel<T, 2, 1, 1, 1>);
+        else if (nt == 2) go(hmatrix_mm_kernel<T, 2, 1, 1, 2>);
+        else if (nt <= 4) go(hmatrix_mm_kernel<T, 2, 2, 2, 2>);
+        else if constexpr (sizeof(T) == 8) go(hmatrix_mm_kernel<T, 2, 2, 2, 4>);
+        else throw std::runtime_error("internal: complex passes hold at most 32 columns");
     }
-    else if (nt <= 1) go(hmatrix_mm_kernel<T, PHASE, 1, MTN, 1>);
-    else if (nt <= 2) go(hmatrix_mm_kernel<T, PHASE, 1, MTN, 2>);
-    else if constexpr (sizeof(T) == 8) go(hmatrix_mm_kernel<T, PHASE, 1, MTN, 4>);
-    else throw std::runtime_error("internal: narrow complex passes hold at most 16 columns");
 }
 
 // Y(:, c0:c0+nc) = beta*Y + alpha*op(A)*X(:, c0:c0+nc) for every pass of <= 64 (32 complex) columns.
@@ -642,7 +654,6 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
     for (int c0 = 0; c0 < mu; c0 += PC) {
         const int nc = std::min(PC, mu - c0), nc8 = (nc + 7) & ~7;
         const int ld = mm_ld(nc, h->es);
-        const bool wide = nc8 > PC / 2;
         const int nt = nc8 / 8;
         // the zero rows (operand of K padding) at this pass's stride; x rows of the pass
         CUDA_CHECK(cudaMemsetAsync(ws + (size_t)po.mm_zero_row * ld, 0, (size_t)kMmZeroRows * ld * sizeof(T), h->stream));
@@ -672,7 +683,7 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
             const MmLaunchCfg c = mm_launch_cfg(1, h->es, po.mm_packet_bytes[0], o.mm1_kg, ld, h->smem_optin);
             p.stream = po.stream[2]; p.stages = po.stages[2]; p.zcopies = po.zcopies[2]; p.units = po.units[2];
             p.n_units = po.n_units[2]; p.counter = h->counters; p.stage_bytes = c.stage_bytes; p.z_rows = c.z_rows; p.n_stages = c.n_stages;
-            launch_mm<T, 1>(wide, nt, (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[2]), c.smem, h->stream, p);
+            launch_mm<T, 1>(nt, (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[2]), c.smem, h->stream, p);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[1], h->stream));
@@ -696,7 +707,7 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
                 p.epoch = peer_ctrl_epoch(pr, peer_buf);
                 p.done  = peer_ctrl_done(pr);
             }
-            launch_mm<T, 2>(wide, nt, (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[3]), c.smem, h->stream, p);
+            launch_mm<T, 2>(nt, (unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[3]), c.smem, h->stream, p);
             h->launches++;
         }
         if (ev) CUDA_CHECK(cudaEventRecord(ev[3], h->stream));
