@@ -95,6 +95,7 @@ struct hmb200_handle {
     std::map<GraphKey, GraphEntry> graphs;
     cudaStream_t cap_stream = nullptr;
     bool use_graphs = true;
+    bool use_pdl = false; // programmatic dependent launches inside a product: opt-in with HMB200_PDL=1 (measured: no gain on top of the CUDA-graph replay, profiles/r02_pdl.md)
     // fused all-gather: one IPC-shared region per rank = [replicated y, buffer 0 | buffer 1 | control block]; the control
     // block holds flags[2][8] (written by the peers), and -- local use only -- epoch[2], the CTA counter and the error word
     struct Peer {
@@ -357,6 +358,7 @@ hmb200_handle *create_impl(const hmb200_flat *flat, int device, void *stream, co
             h->opt.n_stages--;
         h->info = hmb200_info{};
         h->smem_optin = (size_t)prop.sharedMemPerBlockOptin;
+        if (const char *e = std::getenv("HMB200_PDL")) h->use_pdl = std::atoi(e) != 0;
         if (h->opt.build_matmat && !mm_fits(h, h->smem_optin))
             h->opt.build_matmat = 0; // packet sizes chosen by the caller leave no room for two stages of the multi-RHS kernels
         build_op(h, *flat, 'N', h->ops[0]);
@@ -438,6 +440,18 @@ inline double *peer_red_slots(const hmb200_handle::Peer &pr, int q, int parity) 
 }
 inline int *peer_ctrl_err(const hmb200_handle::Peer &pr) { return pr.err_dev; }
 
+// kernel launch as a programmatic dependent of the previous kernel in the stream (PDL); plain launch when `pdl` is false
+template <typename... KArgs, typename... Args>
+void launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl, Args &&...args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...));
+}
+
 // runs out = beta*out + alpha*op(A)*xz[0:n_in] on the handle's stream; x must already be in xz; y is a device pointer;
 // peer_buf >= 0: the phase-2 epilogue also stores the rows into buffer `peer_buf` of every rank and publishes the epoch
 template <typename T>
@@ -469,10 +483,15 @@ void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const doub
         h->launches++;
     }
     if (ev) CUDA_CHECK(cudaEventRecord(ev[1], h->stream));
+    // the kernels after phase 1 are programmatic dependents of their predecessors (PDL): their CTAs are scheduled as SMs free
+    // up and start streaming packets before the predecessor's last CTA has finished; per-kernel events would serialise them
+    const bool pdl = h->use_pdl && !ev;
+    bool prev_kernel = po.n_units[0] > 0;
     if (po.n_reduce > 0) {
         unsigned blocks = (po.n_reduce + 7) / 8;
-        reduce_partials_kernel<T><<<blocks, 256, 0, h->stream>>>(po.reduce, po.n_reduce, (T *)h->xz);
+        launch_kernel(reduce_partials_kernel<T>, dim3(blocks), dim3(256), 0, h->stream, pdl && prev_kernel, (const ReduceSeg *)po.reduce, po.n_reduce, (T *)h->xz);
         h->launches++;
+        prev_kernel = true;
     }
     if (ev) CUDA_CHECK(cudaEventRecord(ev[2], h->stream));
     if (po.n_units[1] > 0) {
@@ -489,7 +508,8 @@ void run_product(hmb200_handle *h, PackedOp &po, const double *alpha, const doub
             p.done  = peer_ctrl_done(pr);
         }
         size_t smem = stream_smem_bytes(2, h->es, o.stage_bytes, o.stage_z_bytes, o.n_stages, o.consumer_warps);
-        hmatrix_stream_kernel<T, 2><<<(unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1]), threads, smem, h->stream>>>(p);
+        p.pdl = (pdl && prev_kernel) ? 1 : 0;
+        launch_kernel(hmatrix_stream_kernel<T, 2>, dim3((unsigned)std::min<uint32_t>((uint32_t)ctas, po.n_units[1])), dim3(threads), smem, h->stream, p.pdl != 0, p);
         h->launches++;
     }
     if (ev) CUDA_CHECK(cudaEventRecord(ev[3], h->stream));
@@ -872,7 +892,8 @@ int fused_product(hmb200_handle *h, const double *alpha, const void *in, void **
     run_cached(h, key, [&] {
         CUDA_CHECK(cudaMemcpyAsync(h->xz, in, in_b, cudaMemcpyDeviceToDevice, h->stream));
         run_product<T>(h, po, alpha, zero, ybuf + (size_t)pr.slab_offset * sizeof(T), nullptr, buf);
-        peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), pr.wait_cycles);
+        launch_kernel(peer_wait_kernel, dim3(1), dim3(32), 0, h->stream, h->use_pdl && !h->timing && po.n_units[1] > 0,
+                      (const unsigned long long *)peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, (const unsigned long long *)peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), pr.wait_cycles);
         h->launches++;
         CUDA_CHECK(cudaGetLastError());
     });

@@ -35,6 +35,8 @@ struct StreamParams {
     const int32_t *out_perm; // optional fused cluster_to_user scatter: y[out_perm[row]] (perm already made local)
     double alpha_re, alpha_im, beta_re, beta_im;
     int stage_bytes, z_bytes, n_stages, consumer_warps;
+    int pdl;                // launched as a programmatic dependent of the previous kernel: the packets (which no kernel writes) start
+                            // streaming at once, the operand slices (x / t, written by the predecessor) wait for griddepcontrol.wait
     // phase 2 only: the all-gather of the row slabs fused into the epilogue.  Every output row is also stored into the
     // replicated vector of each peer GPU (peer-mapped memory over NVLink; pointers already offset to this rank's slab);
     // when the whole grid is done the last CTA publishes this rank's epoch to every rank's flag word (release, system scope).
@@ -77,9 +79,11 @@ __global__ void __launch_bounds__(17 * 32, 1) hmatrix_stream_kernel(const Stream
         ptx::fence_mbar_init();
     }
     __syncthreads();
+    ptx::grid_launch_dependents(); // the next kernel of the product may be scheduled as soon as an SM frees up (no-op without PDL)
 
     if (warp == NW) {
         // ============================== producer warp ==============================
+        bool dep_pending = p.pdl != 0;
         // All schedule metadata is prefetched so that no global-load latency sits on the per-stage critical path:
         //   * the NEXT work unit is claimed (atomicAdd) while the current one streams;
         //   * the 32-byte StageEntry records of a unit are loaded 32 at a time, one per lane, and handed out by shuffles;
@@ -138,6 +142,10 @@ __global__ void __launch_bounds__(17 * 32, 1) hmatrix_stream_kernel(const Stream
                     if (lane == 0) {
                         ptx::mbar_arrive_expect_tx(full_bar(slot), bytes + z_bytes);
                         ptx::bulk_g2s(sbase, p.stream + gmem_off, bytes, full_bar(slot), pol_stream);
+                    }
+                    if (dep_pending) { // first packet under way; everything below reads what the previous kernel wrote
+                        ptx::grid_dependency_wait();
+                        dep_pending = false;
                     }
                     __syncwarp();
                     for (uint32_t b = z_first; b < z_first + n_z; b += 32) {
@@ -334,6 +342,7 @@ __global__ void __launch_bounds__(17 * 32, 1) hmatrix_stream_kernel(const Stream
 // waits until every rank has published at least this rank's own epoch for the buffer (flags: n_ranks words in LOCAL memory
 // written by the peers' phase-2 kernels).  Bounded spin: after ~`max_cycles` clocks the error word is set and the kernel exits.
 __global__ void peer_wait_kernel(const unsigned long long *flags, int n_ranks, const unsigned long long *epoch, int *err, long long max_cycles) {
+    ptx::grid_dependency_wait(); // `epoch` is written by the product kernel in front of this one (no-op without PDL)
     const int q = threadIdx.x;
     if (q >= n_ranks) return;
     const unsigned long long target = *epoch;
@@ -352,6 +361,8 @@ __global__ void peer_wait_kernel(const unsigned long long *flags, int n_ranks, c
 template <typename T>
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const ReduceSeg *segs, uint32_t n_segs, T *xz) {
     using S = Scalar<T>;
+    ptx::grid_launch_dependents();
+    ptx::grid_dependency_wait(); // the partials are written by phase 1 (no-op without PDL)
     const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane   = threadIdx.x & 31;
     if (w >= n_segs) return;
