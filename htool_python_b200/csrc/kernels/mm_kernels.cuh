@@ -584,19 +584,18 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
                     }
                 }
                 ptx::named_bar_sync(1, NW * 32);
-                const uint32_t rows_h = (uint32_t)min(kMmYTileRows, h.rows - hf * kMmYTileRows);
-                const uint32_t nc = (uint32_t)p.ncols, per_tgt = rows_h * nc, total = (uint32_t)(1 + p.n_peers) * per_tgt;
-                for (uint32_t idx = threadIdx.x; idx < total; idx += (uint32_t)NW * 32u) {
-                    const uint32_t tgt = idx / per_tgt, rem = idx - tgt * per_tgt;
-                    const uint32_t r = rem / nc, c = rem - r * nc;
-                    T v = Scalar<T>::mul(alpha, yt[r * ldt + c]);
-                    const size_t o = (size_t)(h.out0 + hf * kMmYTileRows + r) * p.ldy + c;
-                    if (tgt == 0) {
+                // thread -> (column, every 4th row): no divisions; a value is scaled once and stored to the local Y and to every peer
+                const int rows_h = min(kMmYTileRows, h.rows - hf * kMmYTileRows);
+                constexpr int kColSlots = sizeof(T) == 8 ? 64 : 32, kRowStep = NW * 32 / kColSlots;
+                const int c = (int)threadIdx.x % kColSlots;
+                if (c < p.ncols) {
+                    for (int r = (int)threadIdx.x / kColSlots; r < rows_h; r += kRowStep) {
+                        T v = Scalar<T>::mul(alpha, yt[r * ldt + c]);
+                        const size_t o = (size_t)(h.out0 + hf * kMmYTileRows + r) * p.ldy + c;
                         T *y = (T *)p.y;
                         if (!beta_zero) v = Scalar<T>::add(v, Scalar<T>::mul(beta, y[o])); // beta == 0 must not propagate NaNs of y (BLAS)
                         y[o] = v;
-                    } else {
-                        reinterpret_cast<T *>(p.peer_y[tgt - 1])[o] = v; // beta = 0 on the fused path
+                        for (int q = 0; q < p.n_peers; q++) reinterpret_cast<T *>(p.peer_y[q])[o] = v; // beta = 0 on the fused path
                     }
                 }
                 ptx::named_bar_sync(1, NW * 32); // the tile is rewritten by the next half / the next bin
