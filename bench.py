@@ -231,6 +231,14 @@ def run_b200(args):
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the engine has no CPU fallback")
+    bound = []
+    if world > 1 and not os.environ.get("HMB200_BENCH_NO_BIND"):  # like `mpirun --bind-to` for the reference's ranks
+        from htool_python_b200.distributed import bind_to_gpu_cpus
+
+        bound = bind_to_gpu_cpus(local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world)))
+        if bound:
+            thr = max(1, min(thr, len(bound)))
+            os.environ["OMP_NUM_THREADS"] = str(thr)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -449,6 +457,7 @@ def run_b200(args):
                             "launch": "CUDA graph replay of the product (captured by libhmb200.so)" if mu == 1 else "eager",
                             "stored_coefficients_rank0": flat.stored_coefficients, "stored_coefficients_all_ranks": w_all, "leaves_rank0": flat.n_leaves,
                             "assembly": "reference HMatrixTreeBuilder (OpenMP, native generator), outside the timed region", **build_t,
+                            "cpu_binding_rank0": (f"{len(bound)} cores next to the GPU (NVML ideal CPU set, split between the ranks)" if bound else "none"),
                             "e2e_api": ("B200HMatrix.matvec(x, out) on page-locked host numpy buffers, user numbering" if world == 1 else
                                         "B200DistributedOperator.matvec(x, out='shared'): page-locked host x (every rank uploads its 1/P chunk, NVLink exchange); the "
                                         "replicated result lands in ONE node-shared page-locked host vector (every rank downloads its 1/P chunk, host flags)")

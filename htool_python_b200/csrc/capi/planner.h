@@ -23,7 +23,7 @@ struct Options {
     int build_transpose = 0;
     // multi-RHS (DMMA) path
     int build_matmat    = 1;     // also pack the two panel streams of the multi-RHS kernels
-    int mm1_kg          = 4;     // k-groups (8 columns real / 4 complex) per phase-1 packet (even): 128 rows x 32 columns = 32 KiB
+    int mm1_kg          = 6;     // k-groups (8 columns real / 4 complex) per phase-1 packet (even): 128 rows x 48 columns = 48 KiB (measured best at N=1M)
     int mm2_kg          = 8;     // k-groups per phase-2 packet (even): 64 rows x 64 columns = 32 KiB
     int mm_task_cols    = 1024;  // columns of a phase-1 unit; wider source clusters are split and their partial T rows summed
 };

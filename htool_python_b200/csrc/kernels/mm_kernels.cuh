@@ -516,7 +516,11 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
 
     // ============================== consumer warps ==============================
     const int gid = lane >> 2, tig = lane & 3;
-    const int wm = warp % WM, wn = warp / WM;
+    // warp -> (row, column) of the warp grid.  Warps w and w + 4 share a scheduler (and its DMMA pipe); with two warp rows
+    // (tall tiling: a panel of an odd number of m-tiles gives row 0 one tile more than row 1) they are put on DIFFERENT rows, so
+    // that every pipe sees the same number of DMMAs per k-group
+    const int wm = WM == 2 ? ((warp + (warp >> 2)) & 1) : warp % WM;
+    const int wn = WM == 2 ? (warp >> 1) : warp / WM;
     const int c_base = wn * NT * 8;
     const int ncols8 = (p.ncols + 7) & ~7;
     const int nnt    = max(0, min(NT, (ncols8 - c_base) >> 3)); // n-tiles of this warp that hold right-hand sides

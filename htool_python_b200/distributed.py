@@ -98,6 +98,36 @@ def exchange_sum_slabs_(full, offs: List[int], sizes: List[int], out_local, beta
     return out_local
 
 
+def bind_to_gpu_cpus(local_rank: int, local_world: int) -> list:
+    """Pins this process to its share of the host cores next to GPU `local_rank` (NVML's ideal CPU set of the device, split
+    between the ranks whose GPUs report the same set) -- what `mpirun --bind-to` does for the reference's ranks.  One process
+    per GPU with host-synchronous calls is sensitive to scheduler jitter: every collective waits for the slowest rank.
+    Returns the CPU list (empty when NVML or sched_setaffinity is unavailable; nothing is changed then)."""
+    import os
+
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        allowed = sorted(os.sched_getaffinity(0))
+        words = (max(allowed) // 64) + 1
+        sets = []
+        for g in range(local_world):
+            mask = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(g), words)
+            sets.append(tuple(c for c in allowed if (mask[c // 64] >> (c % 64)) & 1))
+        mine = sets[local_rank]
+        if not mine:
+            return []
+        sharers = [g for g in range(local_world) if sets[g] == mine]
+        k, m = sharers.index(local_rank), len(sharers)
+        per = max(1, len(mine) // m)
+        cpus = list(mine[k * per:(k + 1) * per]) or list(mine)
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return []
+
+
 class _RawDeviceArray:
     """`__cuda_array_interface__` view of device memory owned by libhmb200.so (wrapped by torch.as_tensor without a copy)"""
 

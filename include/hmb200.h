@@ -70,7 +70,7 @@ typedef struct hmb200_options {
                                 multi-RHS entry points then fall back to one streamed product per right-hand side) */
     int32_t mm_task_cols;    /* multi-RHS phase 1: source columns per work unit (default 1024); wider clusters are split and their
                                 partial T rows summed */
-    int32_t mm1_kg;          /* multi-RHS phase 1: k-groups (8 columns real / 4 complex) per packet of a 128-row panel (even; default 4) */
+    int32_t mm1_kg;          /* multi-RHS phase 1: k-groups (8 columns real / 4 complex) per packet of a 128-row panel (even; default 6) */
     int32_t mm2_kg;          /* multi-RHS phase 2: k-groups per packet of a 64-row panel (even; default 8) */
     int32_t reserved0;
     int32_t reserved[1];
