@@ -590,10 +590,10 @@ __global__ void __launch_bounds__(kMmThreads, 1) hmatrix_mm_kernel(const MmParam
                 ptx::named_bar_sync(1, NW * 32);
                 // thread -> (column, every 4th row): no divisions; a value is scaled once and stored to the local Y and to every peer
                 const int rows_h = min(kMmYTileRows, h.rows - hf * kMmYTileRows);
-                constexpr int kColSlots = sizeof(T) == 8 ? 64 : 32, kRowStep = NW * 32 / kColSlots;
-                const int c = (int)threadIdx.x % kColSlots;
+                const int cs_log = p.ncols <= 8 ? 3 : (p.ncols <= 16 ? 4 : (p.ncols <= 32 ? 5 : 6)); // column slots: 8 / 16 / 32 / 64
+                const int c = (int)threadIdx.x & ((1 << cs_log) - 1), row_step = (NW * 32) >> cs_log;
                 if (c < p.ncols) {
-                    for (int r = (int)threadIdx.x / kColSlots; r < rows_h; r += kRowStep) {
+                    for (int r = (int)threadIdx.x >> cs_log; r < rows_h; r += row_step) {
                         T v = Scalar<T>::mul(alpha, yt[r * ldt + c]);
                         const size_t o = (size_t)(h.out0 + hf * kMmYTileRows + r) * p.ldy + c;
                         T *y = (T *)p.y;
