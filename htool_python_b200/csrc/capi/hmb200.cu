@@ -681,7 +681,11 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
             const size_t total = (size_t)po.n_in * nc;
             const unsigned g = (unsigned)std::min<size_t>((total + 255) / 256 + 1, 148 * 16);
             if (perm_in) mm_load_rows_kernel<T><<<g, 256, 0, h->stream>>>(x + (size_t)c0 * po.n_in, 0, po.n_in, nc, ws, ld, perm_in, po.n_in);
-            else mm_load_rows_kernel<T><<<g, 256, 0, h->stream>>>(x + c0, mu, po.n_in, nc, ws, ld, nullptr, 0);
+            else {
+                const bool vec_ok = ((uintptr_t)(x + c0) % 16 == 0) && (((size_t)mu * sizeof(T)) % 16 == 0);
+                const unsigned gb = (unsigned)std::min<size_t>(((size_t)po.n_in + 7) / 8, (size_t)h->n_sms * 32);
+                mm_load_rows_fast_kernel<T><<<std::max(gb, 1u), dim3(32, 8), 0, h->stream>>>(x + c0, mu, po.n_in, nc, ws, ld, vec_ok ? 1 : 0);
+            }
             h->launches++;
         }
         CUDA_CHECK(cudaMemsetAsync(h->counters, 0, 64, h->stream));

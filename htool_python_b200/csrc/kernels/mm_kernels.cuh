@@ -684,6 +684,28 @@ __global__ void mm_load_rows_kernel(const T *__restrict__ src, long long lds, in
         ws[i * ld + j] = col_stride > 0 ? src[(size_t)(perm ? perm[i] : (int32_t)i) + (size_t)j * col_stride] : src[i * lds + j];
     }
 }
+// the same for a row-major source without permutation (the operator interface's own layout): one warp per row, 16-byte chunks,
+// no index division -- this copy is pure overhead of the multi-RHS product (the B fragments need the padded row stride) and does
+// not shrink with the number of GPUs, so it has to run at memory speed
+template <typename T>
+__global__ void __launch_bounds__(256) mm_load_rows_fast_kernel(const T *__restrict__ src, long long lds, int n, int ncols, T *__restrict__ ws, int ld, int vec_ok) {
+    constexpr int V = 16 / (int)sizeof(T); // elements per 16-byte chunk
+    const int cpr   = (ncols + V - 1) / V;
+    for (size_t row = (size_t)blockIdx.x * blockDim.y + threadIdx.y; row < (size_t)n; row += (size_t)gridDim.x * blockDim.y) {
+        const T *s = src + row * lds;
+        T *d       = ws + row * ld;
+        for (int c = threadIdx.x; c < cpr; c += blockDim.x) {
+            const int col = c * V;
+            if (vec_ok && col + V <= ncols) {
+                *reinterpret_cast<double2 *>(d + col) = *reinterpret_cast<const double2 *>(s + col);
+            } else {
+#pragma unroll
+                for (int e = 0; e < V; e++)
+                    if (col + e < ncols) d[col + e] = s[col + e];
+            }
+        }
+    }
+}
 // cluster-numbered row-major result rows -> column-major user block (cluster_to_user per column, :202-204)
 template <typename T>
 __global__ void mm_store_user_kernel(const T *__restrict__ yc, int n, int ncols, T *__restrict__ dst, const int32_t *__restrict__ perm, long long col_stride) {
