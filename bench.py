@@ -68,6 +68,8 @@ def parse():
                     "(HPDDM's GMRES with mu > 1 on the multi-RHS product) and column by column, tol 1e-3")
     ap.add_argument("--gmres-args", default="-hpddm_krylov_method gmres -hpddm_schwarz_method none -hpddm_variant right -hpddm_tol 1e-6 -hpddm_gmres_restart 40 -hpddm_max_it 200")
     ap.add_argument("--no-gmres-regularised", action="store_true", help="with --gmres: skip the second solve on the reference's regularised test kernel")
+    ap.add_argument("--transposed", action="store_true", help="also time y = A^T x (and A^H x for complex) on the same operator: adds a 'transposed' object "
+                    "(packs the transposed streams too: twice the device memory)")
     ap.add_argument("--engine-opts", default="", help="k=v,k=v overrides of hmb200_options (tuning runs)")
     a = ap.parse_args()
     preset = CONFIGS.get(a.config or 1)
@@ -268,6 +270,10 @@ def run_b200(args):
 
     tree, H, flat, build_t = assemble(args, world, rank, log)
     opts = {k: int(v) for k, v in (kv.split("=") for kv in args.engine_opts.split(",") if kv)}
+    if args.transposed:
+        opts.setdefault("build_transpose", 1)
+        if args.rhs <= 1:
+            opts.setdefault("no_matmat", 1)
     t0 = time.time()
     if world > 1:
         op = B200DistributedOperator(flat, tree.partition, device=local_rank, fused_allgather=False if os.environ.get("HMB200_NO_FUSED") else None, **opts)
@@ -380,6 +386,11 @@ def run_b200(args):
     sampler.stop()
     shared_result = world > 1 and mu == 1 and getattr(op, "_shm", None) is not None
 
+    # ---- transposed / conjugate-transposed products (trans != 'N' of the operator interface) -----------------------------------
+    tr_obj = None
+    if args.transposed and mu == 1:
+        tr_obj = run_transposed(args, op, engine, H, flat, x_cluster_host, world, rank, dev, thr, barrier, max_over_ranks)
+
     # ---- GMRES with the Krylov basis resident on the device (BASELINE.json configs[4]) --------------------------------
     gm = None
     if args.gmres and mu == 1:
@@ -477,11 +488,57 @@ def run_b200(args):
         }
         if gm is not None:
             line["gmres"] = gm
+        if tr_obj is not None:
+            line["transposed"] = tr_obj
         print(json.dumps(line), flush=True)
     barrier()
     op.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_transposed(args, op, engine, H, flat, x_cluster_host, world, rank, dev, threads, barrier, max_over_ranks):
+    """y = op(A) x for op = transpose (and conjugate transpose for complex operators), device-resident, cluster numbering: one
+    engine call at N = 1; at N > 1 the `trans != 'N'` branch of the global-to-global driver (every rank applies op(A_p) to ITS slab
+    of x, full-length results summed over the ranks: add_distributed_operator_vector_product_global_to_global.hpp:63-84).  Parity:
+    every rank's contribution against the reference's openmp_internal_add_hmatrix_vector_product(trans) of its own slab."""
+    import torch
+
+    import helpers_ref
+
+    n = args.n
+    tdt = torch.complex128 if flat.dtype == "z" else torch.float64
+    o, s = (op.offs[rank], op.sizes[rank]) if world > 1 else (0, n)
+    x_dev = torch.from_numpy(x_cluster_host).to(dev)
+    out = {}
+    for tr in ["T"] + (["C"] if flat.dtype == "z" else []):
+        y = torch.zeros(n, dtype=tdt, device=dev)
+        if world > 1:
+            step = lambda: op.matvec_cluster_transposed_(x_dev, y, tr)  # noqa: E731
+        else:
+            step = lambda: engine.add_vector_product(tr, 1.0, x_dev, 0.0, y)  # noqa: E731
+        for _ in range(args.warmup):
+            step()
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(args.steps):
+            step()
+        ev1.record()
+        barrier()
+        ms = max_over_ranks(ev0.elapsed_time(ev1)) / args.steps
+        rec = {"value": round(1e3 / ms, 3), "unit": UNIT, "ms_per_step": round(ms, 4)}
+        if not args.no_cpu_baseline:  # this rank's contribution op(A_p) x_p against the reference on the same slab
+            part = torch.zeros(n, dtype=tdt, device=dev)
+            engine.add_vector_product(tr, 1.0, x_dev[o:o + s].contiguous(), 0.0, part)
+            ro = helpers_ref.ref_ops()
+            ro.omp_set_num_threads(threads)
+            ref = np.zeros(n, dtype=flat.np_dtype)
+            getattr(ro, "internal_vector_product_addr_" + flat.dtype)(H.address, tr, 1.0, np.ascontiguousarray(x_cluster_host[o:o + s]), 0.0, ref, True)
+            rec["parity_rel_err_vs_reference"] = max_over_ranks(np.linalg.norm(part.cpu().numpy() - ref) / np.linalg.norm(ref))
+        out[tr] = rec
+    out["driver"] = "engine call (1 GPU)" if world == 1 else "op(A_p) x_p on every rank + NCCL all-reduce of the full-length results"
+    return out
 
 
 def gmres_once(solver, dop, b, gargs, barrier):

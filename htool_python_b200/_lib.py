@@ -8,7 +8,10 @@ from pathlib import Path
 from .flat import hmb200_flat
 
 HOST, DEVICE = 0, 1
-LIB_PATH = Path(__file__).resolve().parent / "libhmb200.so"
+import os as _os
+
+# HMB200_LIB: another build of the same ABI (A/B runs of two kernel versions in one GPU session)
+LIB_PATH = Path(_os.environ["HMB200_LIB"]).resolve() if _os.environ.get("HMB200_LIB") else Path(__file__).resolve().parent / "libhmb200.so"
 
 
 class hmb200_options(ctypes.Structure):

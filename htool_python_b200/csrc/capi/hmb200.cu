@@ -95,7 +95,7 @@ struct hmb200_handle {
     std::map<GraphKey, GraphEntry> graphs;
     cudaStream_t cap_stream = nullptr;
     bool use_graphs = true;
-    bool use_pdl = false; // programmatic dependent launches inside a product: opt-in with HMB200_PDL=1 (measured: no gain on top of the CUDA-graph replay, profiles/r02_pdl.md)
+    bool use_pdl = false; // programmatic dependent launches inside a product: opt-in with HMB200_PDL=1 (measured: no gain on top of the CUDA-graph replay, profiles/r02_tried_and_dropped.md)
     // fused all-gather: one IPC-shared region per rank = [replicated y, buffer 0 | buffer 1 | control block]; the control
     // block holds flags[2][8] (written by the peers), and -- local use only -- epoch[2], the CTA counter and the error word
     struct Peer {
