@@ -171,7 +171,7 @@ struct StageBuilder {
 
     StageBuilder(PhasePlan &p, const Options &o, int e) : ph(p), opt(o), es(e), stage_cap((uint32_t)o.stage_bytes), z_cap((uint32_t)o.stage_z_bytes) {}
 
-    uint32_t stage_cap = 0; // packet bytes (opt.stage_bytes, or opt.mm_stage_bytes for the multi-RHS phase-1 stream)
+    uint32_t stage_cap = 0; // packet bytes (opt.stage_bytes)
     uint32_t z_cap     = 0; // operand bytes a packet may reference
     bool fits(uint32_t tile, uint32_t zb) const {
         uint32_t total = 16 + 16 * (n_pieces + 1) + data_bytes + align_up(tile, 16);

@@ -90,7 +90,7 @@ typedef struct hmb200_info {
     double stored_coefficients;           /* W = sum r(m+n) + sum m n, mirrored leaves counted once,
                                              symmetric dense leaves m(n+1)/2 (core/hmatrix/hmatrix_output.hpp:153-208) */
     double pack_seconds, upload_seconds;
-    int64_t mm_stream_bytes, mm_tiles, mm_stages, mm_rows; /* multi-RHS phase-1 stream; workspace rows of the multi-RHS path */
+    int64_t mm_stream_bytes, mm_tiles, mm_stages, mm_rows; /* multi-RHS panel streams (both phases): bytes, phase-1 units, packets; workspace rows of the multi-RHS path */
 } hmb200_info;
 
 /* ---- life cycle ------------------------------------------------------------------------------------------------

@@ -202,3 +202,32 @@ def test_distributed_gmres_two_ranks_gloo():
     assert same
     assert err < 1e-7 and resid < 2e-6, (err, resid)
     assert block == block_ref and err_block < 1e-7, (block, block_ref, err_block)
+
+
+def test_peer_wait_failure_raises_and_poisons_the_operator():
+    """a device-side wait that gave up (error word != 0) must surface at the next host synchronisation point and make the
+    operator refuse further collectives, instead of letting a partly gathered vector through"""
+    import pytest
+
+    from htool_python_b200.distributed import B200DistributedOperator, bind_to_gpu_cpus
+
+    op = object.__new__(B200DistributedOperator)
+    op.fused, op._peer_failed = True, 0
+    status = {"v": 0}
+    op.peer_status = lambda sync=True: status["v"]
+    op.check_peers()  # healthy: nothing happens
+    status["v"] = 3   # rank 2 never published its epoch
+    with pytest.raises(RuntimeError, match="rank 2"):
+        op.check_peers()
+    status["v"] = 0   # the epochs stay out of step: still refused
+    with pytest.raises(RuntimeError, match="must be rebuilt"):
+        op.check_peers()
+    with pytest.raises(RuntimeError):
+        op.matvec_cluster_fused_(None)
+    status["v"] = 104  # an all-reduce wait
+    op2 = object.__new__(B200DistributedOperator)
+    op2.fused, op2._peer_failed = True, 0
+    op2.peer_status = lambda sync=True: status["v"]
+    with pytest.raises(RuntimeError, match="all-reduce, rank 3"):
+        op2.check_peers()
+    assert isinstance(bind_to_gpu_cpus(0, 1), list)  # no NVML here: nothing is changed, empty list

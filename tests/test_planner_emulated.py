@@ -169,3 +169,12 @@ def test_multi_rhs_synthetic_tilings(seed):
     flat = synthetic_flat(rng, m, n, dtype=dtype, max_leaf=int(rng.integers(4, 150)), max_rank=int(rng.integers(1, 150)))
     for opts in MM_OPTION_SETS:
         _check_mm(flat, "N", opts, rng, mu=int(rng.integers(1, 6)))
+
+
+@pytest.mark.parametrize("name,mu", [("d_N_cylinder", 70), ("d_N_rect", 37), ("z_N_sphere", 33), ("z_HL_cylinder", 9)])
+def test_multi_rhs_streams_column_tails_and_passes(name, mu):
+    """several passes of 64 (32 complex) columns, a column tail in the last one, NaN pad columns in the emulated workspace"""
+    flat, _ = load_golden(name)
+    rng = np.random.default_rng(mu)
+    for op in ["N"] + (["T"] if flat.symmetry_for_leaves != "H" else []):
+        _check_mm(flat, op, MM_OPTION_SETS[1], rng, mu)
