@@ -318,8 +318,15 @@ def run_b200(args):
         def step():
             engine.add_vector_product("N", 1.0, x_cluster, 0.0, y_cluster)
             last["y"] = y_cluster
-    if mu > 1:
-        apply_user = lambda: op @ x_user  # noqa: E731
+    if mu > 1 and world > 1:  # page-locked Fortran-ordered block; every rank moves 1/P of the rows of X and Y over PCIe
+        x_blk = torch.empty(n * mu, dtype=tdt).pin_memory().numpy().reshape((n, mu), order="F")
+        x_blk[...] = x_user
+        apply_user = lambda: op.matmat(x_blk, out="shared")  # noqa: E731
+    elif mu > 1:  # page-locked Fortran-ordered blocks: the library DMAs straight from / into them
+        x_blk = torch.empty(n * mu, dtype=tdt).pin_memory().numpy().reshape((n, mu), order="F")
+        x_blk[...] = x_user
+        y_blk = torch.empty(n * mu, dtype=tdt).pin_memory().numpy().reshape((n, mu), order="F")
+        apply_user = lambda: op.matmat(x_blk, out=y_blk)  # noqa: E731
     else:  # page-locked host buffers (torch pin_memory): the library DMAs straight from / into them
         x_pin = torch.from_numpy(np.ascontiguousarray(x_user)).pin_memory().numpy()
         if world > 1:
@@ -384,7 +391,7 @@ def run_b200(args):
     e2e_step = max_over_ranks(time.perf_counter() - t0) / args.steps
     y_user = np.array(y_user, copy=True)
     sampler.stop()
-    shared_result = world > 1 and mu == 1 and getattr(op, "_shm", None) is not None
+    shared_result = world > 1 and ((mu == 1 and getattr(op, "_shm", None) is not None) or (mu > 1 and getattr(op, "_shmb", None) is not None))
 
     # ---- transposed / conjugate-transposed products (trans != 'N' of the operator interface) -----------------------------------
     tr_obj = None
@@ -456,7 +463,7 @@ def run_b200(args):
         replicas_identical = len(set(hs)) == 1
 
     if rank == 0:
-        h2d = es * n * mu * (1 if (world == 1 or (mu == 1 and fused)) else world)
+        h2d = es * n * mu * (1 if (world == 1 or (mu == 1 and fused) or shared_result) else world)
         d2h = es * n * mu * (1 if (world == 1 or shared_result) else world)
         line = {
             "metric": metric_name(args, mu), "value": round(mu * 1e3 / ms_step, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -472,7 +479,9 @@ def run_b200(args):
                             "e2e_api": ("B200HMatrix.matvec(x, out) on page-locked host numpy buffers, user numbering" if world == 1 else
                                         "B200DistributedOperator.matvec(x, out='shared'): page-locked host x (every rank uploads its 1/P chunk, NVLink exchange); the "
                                         "replicated result lands in ONE node-shared page-locked host vector (every rank downloads its 1/P chunk, host flags)")
-                            if mu == 1 else "op @ X on Fortran-ordered host blocks, user numbering"},
+                            if mu == 1 else ("B200HMatrix.matmat(X, out) on page-locked Fortran-ordered host blocks, user numbering" if world == 1 else
+                                             "B200DistributedOperator.matmat(X, out='shared'): page-locked Fortran-ordered X (every rank uploads 1/P of its rows), "
+                                             "result in ONE node-shared page-locked block (every rank downloads 1/P of the rows)")},
             "clocks": clocks,
             "e2e": {"value": round(mu / e2e_step, 3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": round(e2e_step * 1e3, 4)},
             "gpu_launches": int(launches),

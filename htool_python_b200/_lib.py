@@ -49,6 +49,8 @@ EXPORTS = {
     "hmb200_set_global_permutations": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64]),
     "hmb200_matvec_user_chunked_d": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64]),
     "hmb200_matvec_user_chunked_z": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64]),
+    "hmb200_matmat_user_chunked_d": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int]),
+    "hmb200_matmat_user_chunked_z": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int]),
     "hmb200_peer_mm_create": (c_int, [c_void_p, c_int, c_void_p]),
     "hmb200_peer_mm_attach": (c_int, [c_void_p, c_void_p]),
     "hmb200_peer_mm_buffer": (c_int, [c_void_p, c_int, POINTER(c_void_p)]),

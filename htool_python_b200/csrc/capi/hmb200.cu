@@ -661,11 +661,13 @@ void launch_mm(int nt, unsigned grid, size_t smem, cudaStream_t st, const MmPara
 
 // Y(:, c0:c0+nc) = beta*Y + alpha*op(A)*X(:, c0:c0+nc) for every pass of <= 64 (32 complex) columns.
 //   x: device; row-major n_in x mu (perm_in == nullptr), or COLUMN-major user block gathered through perm_in
+//      row_perm != nullptr (row-major x only): row i of the product's input is row row_perm[i] of x (user -> cluster numbering)
 //   y: device, row-major n_out x mu (stride mu)
 //   peer_buf >= 0: the bin epilogue also stores the rows into block `peer_buf` of every rank (row stride mu) and the last pass
 //   publishes the epoch (fused all-gather of the row slabs)
 template <typename T>
-void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, const T *x, const int32_t *perm_in, T *y, int mu, int peer_buf = -1) {
+void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const double *beta, const T *x, const int32_t *perm_in, T *y, int mu, int peer_buf = -1,
+                    const int32_t *row_perm = nullptr) {
     const Options &o = h->opt;
     const int PC = mm_pass_cols(h->es);
     const int ctas = o.ctas > 0 ? o.ctas : h->n_sms;
@@ -684,7 +686,7 @@ void run_mm_product(hmb200_handle *h, PackedOp &po, const double *alpha, const d
             else {
                 const bool vec_ok = ((uintptr_t)(x + c0) % 16 == 0) && (((size_t)mu * sizeof(T)) % 16 == 0);
                 const unsigned gb = (unsigned)std::min<size_t>(((size_t)po.n_in + 7) / 8, (size_t)h->n_sms * 32);
-                mm_load_rows_fast_kernel<T><<<std::max(gb, 1u), dim3(32, 8), 0, h->stream>>>(x + c0, mu, po.n_in, nc, ws, ld, vec_ok ? 1 : 0);
+                mm_load_rows_fast_kernel<T><<<std::max(gb, 1u), dim3(32, 8), 0, h->stream>>>(x + c0, mu, po.n_in, nc, ws, ld, vec_ok ? 1 : 0, row_perm);
             }
             h->launches++;
         }
@@ -1013,6 +1015,67 @@ int user_matvec_chunked(hmb200_handle *h, const void *x_host, int64_t c0, int64_
     return 0;
 }
 
+// rows [r0, r0 + rcnt) of Y_user = A X_user on every rank, from this rank's rows [c0, c0 + cnt) of the replicated column-major
+// user block X: strided H2D of the chunk, layout change to rows, all-gather of the chunks over the multi-RHS peer blocks, row
+// gather to cluster numbering fused into the workspace load, slab product with the fused all-gather of its rows, gather of the
+// rank's chunk of the user-numbered result, strided D2H.  The distributed matrix product of
+// add_distributed_operator_matrix_product_global_to_global.hpp:138-280 with n mu / P elements per rank and direction over PCIe.
+template <typename T>
+int user_matmat_chunked(hmb200_handle *h, const void *x_host, int64_t ldx, int64_t c0, int64_t cnt, void *y_host, int64_t ldy, int64_t r0, int64_t rcnt, int mu) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    hmb200_handle::Peer &pr = h->peer;
+    if (!pr.attached || !pr.mm_attached) throw std::runtime_error("hmb200_peer_attach / hmb200_peer_mm_attach have not been called");
+    if (mu != pr.mm_mu) throw std::runtime_error("the replicated blocks were created for another number of right-hand sides");
+    if (!h->gperm_s || !h->ginv_t) throw std::runtime_error("hmb200_set_global_permutations has not been called");
+    PackedOp &po = h->ops[0];
+    if (!po.has_mm) throw std::runtime_error("the multi-RHS streams were not packed (no_matmat)");
+    if ((int64_t)po.n_in != pr.n_global) throw std::runtime_error("the chunked user-numbering product needs a square operator");
+    if (c0 < 0 || cnt < 0 || c0 + cnt > pr.n_global || r0 < 0 || rcnt < 0 || r0 + rcnt > pr.n_global || ldx < cnt || ldy < rcnt) throw std::runtime_error("chunk outside the block");
+    if ((cnt && !host_is_pinned((const T *)x_host + c0)) || (rcnt && !host_is_pinned((T *)y_host + r0))) throw std::runtime_error("the host blocks must be page-locked (cudaHostAlloc / cudaHostRegister)");
+    const int buf_x = (int)(pr.products & 1);
+    pr.products++;
+    const int buf_y = (int)(pr.products & 1);
+    pr.products++;
+    const uint64_t chunk = (uint64_t)std::max<int64_t>(std::max(cnt, rcnt), 1) * mu;
+    ensure_dev(&h->xbuf, &h->xbuf_elems, 2 * chunk, h->es); // [column-major chunk | the same as rows]
+    ensure_dev(&h->ybuf2, &h->ybuf2_elems, chunk, h->es);
+    T *xcol = (T *)h->xbuf, *xrow = xcol + chunk, *ycol = (T *)h->ybuf2;
+    if (cnt) {
+        CUDA_CHECK(cudaMemcpy2DAsync(xcol, (size_t)cnt * sizeof(T), (const T *)x_host + c0, (size_t)ldx * sizeof(T), (size_t)cnt * sizeof(T), (size_t)mu, cudaMemcpyHostToDevice, h->stream));
+        const unsigned g = (unsigned)std::min<size_t>(((size_t)cnt * mu + 255) / 256 + 1, 148 * 16);
+        mm_load_rows_kernel<T><<<g, 256, 0, h->stream>>>(xcol, 0, (int)cnt, mu, xrow, mu, nullptr, cnt); // column-major chunk -> rows
+    }
+    {   // all-gather of the row chunks (user numbering) into block buf_x of every rank
+        PeerGatherParams p{};
+        p.src = xrow; p.n_local = cnt * mu; p.n_targets = pr.n_ranks;
+        for (int q = 0; q < pr.n_ranks; q++) {
+            p.dst[q]   = pr.mm_region[q] + (size_t)buf_x * pr.mm_buf_bytes + (size_t)c0 * mu * sizeof(T);
+            p.flags[q] = peer_ctrl_flags(pr, q, buf_x) + pr.rank;
+        }
+        p.epoch = peer_ctrl_epoch(pr, buf_x);
+        p.done  = peer_ctrl_done(pr);
+        const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>((cnt * mu + 2047) / 2048, 4 * h->n_sms));
+        peer_gather_kernel<T><<<grid, 256, 0, h->stream>>>(p);
+        peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf_x), pr.n_ranks, peer_ctrl_epoch(pr, buf_x), peer_ctrl_err(pr), pr.wait_cycles);
+    }
+    const T *xu = reinterpret_cast<const T *>(pr.mm_region[pr.rank] + (size_t)buf_x * pr.mm_buf_bytes);
+    T *yb       = reinterpret_cast<T *>(pr.mm_region[pr.rank] + (size_t)buf_y * pr.mm_buf_bytes);
+    const double one[2] = {1.0, 0.0}, zero[2] = {0.0, 0.0};
+    run_mm_product<T>(h, po, one, zero, xu, nullptr, yb + (size_t)pr.slab_offset * mu, mu, buf_y, h->gperm_s);
+    peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf_y), pr.n_ranks, peer_ctrl_epoch(pr, buf_y), peer_ctrl_err(pr), pr.wait_cycles);
+    if (rcnt) {
+        const unsigned g = (unsigned)std::min<size_t>(((size_t)rcnt * mu + 255) / 256 + 1, 148 * 16);
+        mm_gather_user_chunk_kernel<T><<<g, 256, 0, h->stream>>>(yb, mu, h->ginv_t, r0, (int)rcnt, ycol);
+        CUDA_CHECK(cudaMemcpy2DAsync((T *)y_host + r0, (size_t)ldy * sizeof(T), ycol, (size_t)rcnt * sizeof(T), (size_t)rcnt * sizeof(T), (size_t)mu, cudaMemcpyDeviceToHost, h->stream));
+    }
+    h->launches += 6;
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaStreamSynchronize(h->stream));
+    const int err = *(volatile int *)pr.err_host;
+    if (err) throw std::runtime_error("a peer did not arrive within the wait bound (status " + std::to_string(err) + ")");
+    return 0;
+}
+
 template <typename F>
 int guarded(F &&f) {
     try {
@@ -1234,6 +1297,12 @@ int hmb200_matvec_user_chunked_d(hmb200_handle *h, const double *x_chunk, int64_
 }
 int hmb200_matvec_user_chunked_z(hmb200_handle *h, const double *x_chunk, int64_t c0, int64_t count, double *y_chunk, int64_t r0, int64_t rcount) {
     return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return user_matvec_chunked<double2>(h, x_chunk, c0, count, y_chunk, r0, rcount); });
+}
+int hmb200_matmat_user_chunked_d(hmb200_handle *h, const double *X, int64_t ldx, int64_t c0, int64_t count, double *Y, int64_t ldy, int64_t r0, int64_t rcount, int mu) {
+    return guarded([&] { if (!h || h->es != 8) throw std::runtime_error("handle is not a real (double) engine"); return user_matmat_chunked<double>(h, X, ldx, c0, count, Y, ldy, r0, rcount, mu); });
+}
+int hmb200_matmat_user_chunked_z(hmb200_handle *h, const double *X, int64_t ldx, int64_t c0, int64_t count, double *Y, int64_t ldy, int64_t r0, int64_t rcount, int mu) {
+    return guarded([&] { if (!h || h->es != 16) throw std::runtime_error("handle is not a complex engine"); return user_matmat_chunked<double2>(h, X, ldx, c0, count, Y, ldy, r0, rcount, mu); });
 }
 int hmb200_peer_buffer(hmb200_handle *h, int index, void **ptr) {
     if (!h || !ptr || index < 0 || index > 1 || !h->peer.region[h->peer.rank]) { g_last_error = "no peer region / bad index"; return 1; }

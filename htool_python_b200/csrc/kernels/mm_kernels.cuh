@@ -688,11 +688,12 @@ __global__ void mm_load_rows_kernel(const T *__restrict__ src, long long lds, in
 // no index division -- this copy is pure overhead of the multi-RHS product (the B fragments need the padded row stride) and does
 // not shrink with the number of GPUs, so it has to run at memory speed
 template <typename T>
-__global__ void __launch_bounds__(256) mm_load_rows_fast_kernel(const T *__restrict__ src, long long lds, int n, int ncols, T *__restrict__ ws, int ld, int vec_ok) {
+__global__ void __launch_bounds__(256) mm_load_rows_fast_kernel(const T *__restrict__ src, long long lds, int n, int ncols, T *__restrict__ ws, int ld, int vec_ok,
+                                                                const int32_t *__restrict__ row_perm) {
     constexpr int V = 16 / (int)sizeof(T); // elements per 16-byte chunk
     const int cpr   = (ncols + V - 1) / V;
     for (size_t row = (size_t)blockIdx.x * blockDim.y + threadIdx.y; row < (size_t)n; row += (size_t)gridDim.x * blockDim.y) {
-        const T *s = src + row * lds;
+        const T *s = src + (row_perm ? (size_t)row_perm[row] : row) * lds; // optional row gather (user -> cluster numbering)
         T *d       = ws + row * ld;
         for (int c = threadIdx.x; c < cpr; c += blockDim.x) {
             const int col = c * V;
@@ -704,6 +705,18 @@ __global__ void __launch_bounds__(256) mm_load_rows_fast_kernel(const T *__restr
                     if (col + e < ncols) d[col + e] = s[col + e];
             }
         }
+    }
+}
+// rows [r0, r0 + cnt) of the USER-numbered result as a column-major chunk (cnt x ncols, leading dimension cnt), gathered from the
+// cluster-numbered row-major block through the inverse target permutation: the rank's share of the replicated result of the
+// distributed matrix product, ready for one strided D2H copy
+template <typename T>
+__global__ void mm_gather_user_chunk_kernel(const T *__restrict__ yc, int ncols, const int32_t *__restrict__ inv_perm, long long r0, int cnt, T *__restrict__ dst) {
+    const size_t total = (size_t)cnt * ncols;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const size_t i = t / ncols;
+        const int j    = (int)(t - i * ncols);
+        dst[i + (size_t)j * cnt] = yc[(size_t)inv_perm[r0 + i] * ncols + j];
     }
 }
 // cluster-numbered row-major result rows -> column-major user block (cluster_to_user per column, :202-204)

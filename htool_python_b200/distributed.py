@@ -655,6 +655,152 @@ class B200DistributedOperator:
         except Exception:
             return None
 
+    def _setup_shared_block(self, mu: int):
+        """node-shared page-locked result blocks (two, n_target x mu column-major) for `matmat`; collective.  Returns False (and
+        keeps the per-rank full transfer) when the shared memory cannot be set up on every rank."""
+        from multiprocessing import resource_tracker, shared_memory
+
+        import torch
+        import torch.distributed as dist
+
+        old = getattr(self, "_shmb", None)
+        if old is not None and old["mu"] == mu:
+            return True
+        self._release_shared_block()
+        blk = (self.n_target * mu * self.es + 4095) // 4096 * 4096
+        nbytes = 4096 + 2 * blk
+        name, shm, base = [None], None, None
+        if self.rank == 0:
+            try:
+                shm = shared_memory.SharedMemory(create=True, size=nbytes)
+                np.frombuffer(shm.buf, dtype=np.uint8, count=4096)[:] = 0
+                name[0] = shm.name
+            except Exception:
+                shm = None
+        dist.broadcast_object_list(name, src=dist.get_global_rank(self.group, 0) if self.group is not None else 0, group=self.group)
+        ok = name[0] is not None
+        if ok and self.rank != 0:
+            try:
+                shm = shared_memory.SharedMemory(name=name[0])
+                try:
+                    resource_tracker.unregister(shm._name, "shared_memory")
+                except Exception:
+                    pass
+            except Exception:
+                ok = False
+        if ok:
+            base = np.frombuffer(shm.buf, dtype=np.uint8)
+            with torch.cuda.device(self.device):
+                ok = int(torch.cuda.cudart().cudaHostRegister(base.ctypes.data, nbytes, 0)) == 0
+        oks = [None] * self.world
+        dist.all_gather_object(oks, bool(ok), group=self.group)
+        if not all(oks):
+            if ok:
+                torch.cuda.cudart().cudaHostUnregister(base.ctypes.data)
+            if shm is not None:
+                shm.close()
+                if self.rank == 0:
+                    shm.unlink()
+            return False
+        self._shmb = {"mu": mu, "shm": shm, "base": base, "calls": 0,
+                      "flags": np.frombuffer(shm.buf, dtype=np.int64, count=512)[::8][:self.world],
+                      "Y": [np.frombuffer(shm.buf, dtype=self.np_dtype, count=self.n_target * mu, offset=4096 + b * blk).reshape((self.n_target, mu), order="F") for b in range(2)],
+                      "pin_x": None}
+        return True
+
+    def _release_shared_block(self):
+        blk = getattr(self, "_shmb", None)
+        if blk is None:
+            return
+        import torch
+
+        try:
+            torch.cuda.current_stream(self.device).synchronize()
+            torch.cuda.cudart().cudaHostUnregister(blk["base"].ctypes.data)
+        except Exception:
+            pass
+        shm = blk["shm"]
+        blk["flags"] = blk["Y"] = blk["base"] = None
+        self._shmb = None
+        try:
+            shm.close()
+            if self.rank == 0:
+                shm.unlink()
+        except Exception:
+            pass
+
+    def matmat(self, X, out=None):
+        """`A @ X` for a Fortran-ordered (n_source, mu) host block in user numbering.  On several ranks of one node (peer regions
+        set up, square operator) every rank uploads its 1/P of the ROWS of X and downloads its 1/P of the rows of Y
+        (hmb200_matmat_user_chunked_*); the result lands in a node-shared page-locked block that `out="shared"` returns without
+        a copy (valid until the call after the next).  Page-locked X is DMA'd directly, pageable X goes through a pinned chunk."""
+        import time
+
+        import torch
+
+        X = np.asarray(X)
+        if X.ndim != 2:
+            raise RuntimeError("Wrong dimension for HMatrix-matrix product")
+        if X.shape[0] != self.n_source:
+            raise RuntimeError("Wrong size for HMatrix-matrix product")
+        mu = int(X.shape[1])
+        chunked = (self.fused and self.world > 1 and self.n_source == self.n_target and getattr(self, "_shm", None) is not None
+                   and self.engine.info["mm_stream_bytes"] > 0 and mu > 1)
+        if chunked:
+            if getattr(self, "_mm_mu", 0) != mu:
+                self._setup_fused_matmat(mu)
+            chunked = self._setup_shared_block(mu)
+        if not chunked:
+            Y = self.__matmul__(X)
+            if isinstance(out, np.ndarray):
+                np.copyto(out, Y)
+                return out
+            return Y
+        if self._peer_failed:
+            self.check_peers()
+        blk = self._shmb
+        k = blk["calls"]
+        blk["calls"] += 1
+        n, es = self.n_source, self.es
+        c0, c1 = self.rank * n // self.world, (self.rank + 1) * n // self.world
+        fn = _lib.lib().hmb200_matmat_user_chunked_z if self.is_complex else _lib.lib().hmb200_matmat_user_chunked_d
+        self.engine.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+        Y = blk["Y"][k & 1]
+        if X.dtype == self.np_dtype and X.flags.f_contiguous and self._is_pinned(X):
+            xptr, ldx = X.ctypes.data, n  # page-locked block: strided DMA straight from it
+        else:
+            # pageable X: stage this rank's rows of every column in a pinned (c1 - c0) x mu block.  The library addresses element
+            # (i, j) as base + i + j*ld and reads rows [c0, c1), so pass base = stage - c0 elements and ld = c1 - c0
+            if blk["pin_x"] is None or blk["pin_x"].numel() < (c1 - c0) * mu:
+                blk["pin_x"] = torch.empty((c1 - c0) * mu, dtype=self.torch_dtype).pin_memory()
+            stage = blk["pin_x"].numpy()[:(c1 - c0) * mu].reshape((c1 - c0, mu), order="F")
+            stage[...] = X[c0:c1, :]
+            xptr, ldx = stage.ctypes.data - es * c0, c1 - c0
+        st = fn(self.engine._h, xptr, ldx, c0, c1 - c0, Y.ctypes.data, n, c0, c1 - c0, mu)
+        if st != 0:
+            self._peer_failed = self._peer_failed or self.peer_status(sync=False) or 1
+            _lib.check(st)
+        fl = blk["flags"]
+        fl[self.rank] = k + 1
+        t0 = time.perf_counter()
+        while int(fl.min()) < k + 1:
+            if time.perf_counter() - t0 > self.shared_result_timeout_s:
+                raise RuntimeError(f"hmb200: rank {int(fl.argmin())} did not deliver its rows of the result within {self.shared_result_timeout_s} s")
+        if isinstance(out, str):
+            return Y
+        if out is None:
+            return np.array(Y, order="F")
+        np.copyto(out, Y)
+        return out
+
+    def _is_pinned(self, a) -> bool:
+        import torch
+
+        try:
+            return bool(torch.from_numpy(a.reshape(-1, order="F") if a.ndim == 2 else a).is_pinned())
+        except Exception:
+            return False
+
     def __matmul__(self, X):
         """X: (n_source, mu) Fortran-ordered like the reference (distributed_operator.hpp:39-65); result F-ordered."""
         import torch
@@ -682,6 +828,7 @@ class B200DistributedOperator:
         return np.array(pin_y.numpy().reshape((self.n_target, mu), order="F"), order="F")
 
     def close(self):
+        self._release_shared_block()
         shm = getattr(self, "_shm", None)
         if shm is not None:
             import torch

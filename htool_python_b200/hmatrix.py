@@ -76,5 +76,19 @@ class B200HMatrix:
         X = np.asfortranarray(X, dtype=self._np_dtype)
         return self.engine.matmat_user(X)
 
+    def matmat(self, X, out=None):
+        """`H @ X` writing into the caller's Fortran-ordered `out` (user numbering).  With page-locked blocks the library DMAs
+        straight from / into them (no host-side copy, no fresh allocation per call); see `matvec`."""
+        X = np.asarray(X)
+        if X.ndim != 2:
+            raise RuntimeError("Wrong dimension for HMatrix-matrix product")
+        if X.shape[0] != self.shape[1]:
+            raise RuntimeError("Wrong size for HMatrix-matrix product")
+        if X.dtype != self._np_dtype or not X.flags.f_contiguous:
+            X = np.asfortranarray(X, dtype=self._np_dtype)
+        if out is not None and (not isinstance(out, np.ndarray) or out.dtype != self._np_dtype or out.shape != (self.shape[0], X.shape[1]) or not out.flags.f_contiguous):
+            raise ValueError("out must be a Fortran-ordered numpy array of the operator's dtype and shape (n_target, mu)")
+        return self.engine.matmat_user(X, out)
+
     def close(self):
         self.engine.close()

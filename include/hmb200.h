@@ -172,6 +172,13 @@ int hmb200_matrix_product_allgather_z(hmb200_handle *h, const double *alpha, con
 int hmb200_set_global_permutations(hmb200_handle *h, const int32_t *source_perm, int64_t n_source, const int32_t *inverse_target_perm, int64_t n_target);
 int hmb200_matvec_user_chunked_d(hmb200_handle *h, const double *x_chunk, int64_t c0, int64_t count, double *y_chunk, int64_t r0, int64_t rcount);
 int hmb200_matvec_user_chunked_z(hmb200_handle *h, const double *x_chunk, int64_t c0, int64_t count, double *y_chunk, int64_t r0, int64_t rcount);
+/* the same for column-major blocks of mu right-hand sides in user numbering (DistributedOperator.__matmul__,
+ * core/distributed_operator/linalg/add_distributed_operator_matrix_product_global_to_global.hpp:138-280): X / Y are the BASES of
+ * the page-locked host blocks (element (i, j) at i + j*ld; only the rows named below are touched), every rank uploads rows [c0, c0+count) of X and
+ * downloads rows [r0, r0+rcount) of Y (all columns).  Needs hmb200_peer_mm_create / _attach for this mu.  Synchronous; counts as
+ * two collectives. */
+int hmb200_matmat_user_chunked_d(hmb200_handle *h, const double *X, int64_t ldx, int64_t c0, int64_t count, double *Y, int64_t ldy, int64_t r0, int64_t rcount, int mu);
+int hmb200_matmat_user_chunked_z(hmb200_handle *h, const double *X, int64_t ldx, int64_t c0, int64_t count, double *Y, int64_t ldy, int64_t r0, int64_t rcount, int mu);
 /* the solver's two collectives on the same peer regions (no NCCL / MPI on the iteration path):
  *   hmb200_peer_allgather     local slab (n_rows elements, device) -> replicated vector on every rank
  *                             (MPI_Allgatherv of ..._vector_product_local_to_local.hpp:44); counts as one collective of step 3

@@ -272,6 +272,14 @@ def _dist_worker(rank, world, port, q, kernel="laplace_reg"):
             for _ in range(3):
                 same = same and np.array_equal(np.array(op.matvec(x, out="shared")), y)
             same = same and getattr(op, "_shm", None) is not None
+            # blocks: every rank moves 1/P of the rows of X and Y over PCIe (hmb200_matmat_user_chunked_*), node-shared result block;
+            # pageable X (staged chunk), page-locked X (strided DMA), a second width (blocks re-created)
+            for _ in range(2):
+                same = same and np.array_equal(np.array(op.matmat(X, out="shared")), Y)
+            Xp = torch.empty(n * 70, dtype=op.torch_dtype).pin_memory().numpy().reshape((n, 70), order="F")
+            Xp[...] = X70
+            same = same and np.array_equal(op.matmat(Xp), Y70) and np.array_equal(np.array(op.matmat(X, out="shared")), Y)
+            same = same and getattr(op, "_shmb", None) is not None
         status = op.peer_status() if op.fused else 0
         # transposed / conjugate-transposed distributed product: sum over the ranks of op(A_p) x_p (all-reduce driver)
         import torch
@@ -627,3 +635,29 @@ def test_fused_allgather_protocol_single_rank():
     assert op.peer_status() == 0
     assert rel_err(op * z["x"], z["y_ref"]) < TOL
     op.close()
+
+
+def test_hmatrix_matmat_into_caller_buffers():
+    """B200HMatrix.matmat(X, out): page-locked Fortran-ordered blocks are DMA'd directly; same bits as `@`; shape / layout checks"""
+    import torch
+
+    from htool_python_b200 import B200HMatrix
+
+    flat, _ = load_golden("d_N_cylinder")
+    hb = B200HMatrix(flat)
+    rng = np.random.default_rng(5)
+    n, m, mu = flat.n_cols, flat.n_rows, 7
+    X = np.asfortranarray(helpers.rand_vec(rng, n, flat.np_dtype, mu))
+    Y_ref = hb @ X
+    Xp = torch.empty(n * mu, dtype=torch.float64).pin_memory().numpy().reshape((n, mu), order="F")
+    Yp = torch.empty(m * mu, dtype=torch.float64).pin_memory().numpy().reshape((m, mu), order="F")
+    Xp[...] = X
+    Yp[...] = np.nan
+    out = hb.matmat(Xp, out=Yp)
+    assert out is Yp and np.array_equal(Yp, Y_ref)
+    assert np.array_equal(hb.matmat(X), Y_ref)
+    with pytest.raises(ValueError):
+        hb.matmat(X, out=np.zeros((m, mu)))  # C-ordered
+    with pytest.raises(RuntimeError, match="Wrong size"):
+        hb.matmat(X[:-1])
+    hb.close()
