@@ -1390,10 +1390,10 @@ static int permute_impl(bool gather, const int32_t *perm, int off, int n, const 
         const void *din = in;
         void *dout = out;
         int32_t *tp = nullptr; void *ti = nullptr, *to = nullptr;
-        if (mem == HMB200_HOST) {
-            CUDA_CHECK(cudaMalloc(&tp, sizeof(int32_t) * (size_t)(off + n)));
-            CUDA_CHECK(cudaMalloc(&ti, bytes));
-            CUDA_CHECK(cudaMalloc(&to, bytes));
+        if (mem == HMB200_HOST) { // staging from the stream-ordered pool: after the first call no allocation reaches the driver
+            CUDA_CHECK(cudaMallocAsync((void **)&tp, sizeof(int32_t) * (size_t)(off + n), s));
+            CUDA_CHECK(cudaMallocAsync(&ti, bytes, s));
+            CUDA_CHECK(cudaMallocAsync(&to, bytes, s));
             CUDA_CHECK(cudaMemcpyAsync(tp, perm, sizeof(int32_t) * (size_t)(off + n), cudaMemcpyHostToDevice, s));
             CUDA_CHECK(cudaMemcpyAsync(ti, in, bytes, cudaMemcpyHostToDevice, s));
             dperm = tp; din = ti; dout = to;
@@ -1410,8 +1410,8 @@ static int permute_impl(bool gather, const int32_t *perm, int off, int n, const 
         CUDA_CHECK(cudaGetLastError());
         if (mem == HMB200_HOST) {
             CUDA_CHECK(cudaMemcpyAsync(out, to, bytes, cudaMemcpyDeviceToHost, s));
+            cudaFreeAsync(tp, s); cudaFreeAsync(ti, s); cudaFreeAsync(to, s);
             CUDA_CHECK(cudaStreamSynchronize(s));
-            cudaFree(tp); cudaFree(ti); cudaFree(to);
         }
         return 0;
     });
