@@ -59,6 +59,7 @@ EXPORTS = {
     "hmb200_peer_allgather": (c_int, [c_void_p, c_void_p, POINTER(c_void_p)]),
     "hmb200_peer_allgather_range": (c_int, [c_void_p, c_void_p, c_int64, c_int64, POINTER(c_void_p)]),
     "hmb200_peer_allreduce_f64": (c_int, [c_void_p, c_void_p, c_int]),
+    "hmb200_peer_exchange_sum": (c_int, [c_void_p, c_char, c_void_p, c_void_p, c_void_p, c_void_p]),
     "hmb200_vector_product_allgather_d": (c_int, [c_void_p, c_void_p, c_void_p, POINTER(c_void_p)]),
     "hmb200_vector_product_allgather_z": (c_int, [c_void_p, c_void_p, c_void_p, POINTER(c_void_p)]),
     "hmb200_permute_gather": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),

@@ -13,6 +13,8 @@
 #include <map>
 #include <stdexcept>
 #include <string>
+#include <algorithm>
+#include <iterator>
 #include <vector>
 
 using namespace hmb200;
@@ -91,8 +93,10 @@ struct hmb200_handle {
         char op; const void *in; void *out; double a[2], b[2]; int fused;
         bool operator<(const GraphKey &o) const { return std::memcmp(this, &o, sizeof(GraphKey)) < 0; }
     };
-    struct GraphEntry { cudaGraphExec_t exec = nullptr; int64_t launches = 0; int seen = 0; };
+    struct GraphEntry { cudaGraphExec_t exec = nullptr; int64_t launches = 0; int seen = 0; uint64_t last_use = 0; };
     std::map<GraphKey, GraphEntry> graphs;
+    uint64_t graph_tick = 0;
+    static constexpr size_t kMaxGraphKeys = 256;
     cudaStream_t cap_stream = nullptr;
     bool use_graphs = true;
     bool use_pdl = false; // programmatic dependent launches inside a product: opt-in with HMB200_PDL=1 (measured: no gain on top of the CUDA-graph replay, profiles/r02_tried_and_dropped.md)
@@ -542,6 +546,25 @@ void clear_graphs(hmb200_handle *h) {
     h->graphs.clear();
 }
 
+// the cache is full: forget the keys seen once (one-off pointers, no graph yet), then the least recently used half of the rest.
+// Replaying callers (a solver cycling through a few buffers) keep their graphs however many one-off pointers pass by.
+void trim_graphs(hmb200_handle *h) {
+    for (auto it = h->graphs.begin(); it != h->graphs.end();)
+        it = it->second.exec ? std::next(it) : h->graphs.erase(it);
+    if (h->graphs.size() <= hmb200_handle::kMaxGraphKeys / 2) return;
+    std::vector<uint64_t> ticks;
+    ticks.reserve(h->graphs.size());
+    for (auto &kv : h->graphs) ticks.push_back(kv.second.last_use);
+    std::nth_element(ticks.begin(), ticks.begin() + ticks.size() / 2, ticks.end());
+    const uint64_t keep_from = ticks[ticks.size() / 2];
+    for (auto it = h->graphs.begin(); it != h->graphs.end();) {
+        if (it->second.last_use < keep_from) {
+            cudaGraphExecDestroy(it->second.exec); // stream-ordered after the launches already enqueued
+            it = h->graphs.erase(it);
+        } else ++it;
+    }
+}
+
 // issues `issue()` (a stream-ordered sequence on h->stream without host synchronisation) either eagerly or -- from the second
 // time `key` is seen -- as a replay of a CUDA graph captured on a private stream
 template <typename F>
@@ -558,8 +581,9 @@ void run_cached(hmb200_handle *h, const hmb200_handle::GraphKey &key, F &&issue)
             return;
         }
     }
-    if (h->graphs.size() > 256) clear_graphs(h);
+    if (h->graphs.size() > hmb200_handle::kMaxGraphKeys && !h->graphs.count(key)) trim_graphs(h);
     auto &ge = h->graphs[key];
+    ge.last_use = ++h->graph_tick;
     if (!ge.exec && ++ge.seen < 2 && key.fused == 0) {
         issue(); // first use of a key runs eagerly (one-off pointers never pay for a capture); fused products always recur
         return;
@@ -931,6 +955,43 @@ int peer_allgather(hmb200_handle *h, const void *local_slab, void **y_out, int64
     h->launches += 2;
     CUDA_CHECK(cudaGetLastError());
     if (y_out) *y_out = pr.region[pr.rank] + (size_t)buf * pr.buf_bytes;
+    return 0;
+}
+
+// y_local = beta * y_local + sum over the ranks q (ascending) of [alpha * op(A_q) x_q] restricted to this rank's slab: the transposed
+// local-to-local product.  The rank's full-length contribution goes into ITS OWN replicated buffer, the epoch is published, and
+// after the wait a kernel pulls the rank's slab of every contribution over NVLink.  Same buffers, epochs and alternation as the
+// fused all-gather, so the two can be mixed freely: a rank overwrites a buffer only after the wait of the product in between,
+// i.e. after every peer has finished reading it.
+template <typename T>
+int peer_exchange_sum(hmb200_handle *h, char trans, const double *alpha, const void *x_local, const double *beta, void *y_local) {
+    CUDA_CHECK(cudaSetDevice(h->device));
+    hmb200_handle::Peer &pr = h->peer;
+    if (!pr.attached) throw std::runtime_error("hmb200_peer_attach has not been called");
+    if (trans != 'T' && trans != 'C') throw std::runtime_error("trans must be 'T' or 'C'");
+    PackedOp &po = select_op(h, trans);
+    if (po.n_out != pr.n_global || po.n_in != h->n_rows) throw std::runtime_error("the transposed exchange needs a square operator whose columns are the replicated vector");
+    const int buf = (int)(pr.products & 1);
+    pr.products++;
+    uint8_t *ybuf = pr.region[pr.rank] + (size_t)buf * pr.buf_bytes;
+    const double zero[2] = {0.0, 0.0};
+    vector_product<T>(h, trans, alpha, x_local, zero, ybuf, HMB200_DEVICE);
+    PeerGatherParams g{};
+    g.n_targets = pr.n_ranks;
+    for (int q = 0; q < pr.n_ranks; q++) g.flags[q] = peer_ctrl_flags(pr, q, buf) + pr.rank;
+    g.epoch = peer_ctrl_epoch(pr, buf);
+    peer_publish_kernel<<<1, 32, 0, h->stream>>>(g);
+    peer_wait_kernel<<<1, 32, 0, h->stream>>>(peer_ctrl_flags(pr, pr.rank, buf), pr.n_ranks, peer_ctrl_epoch(pr, buf), peer_ctrl_err(pr), pr.wait_cycles);
+    PeerSumParams sp{};
+    sp.n_ranks = pr.n_ranks;
+    sp.n = h->n_rows;
+    for (int q = 0; q < pr.n_ranks; q++) sp.src[q] = pr.region[q] + (size_t)buf * pr.buf_bytes + (size_t)pr.slab_offset * sizeof(T);
+    sp.out = y_local;
+    sp.beta[0] = beta[0]; sp.beta[1] = h->es == 16 ? beta[1] : 0.0;
+    const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(((int64_t)h->n_rows + 255) / 256, 148 * 4));
+    peer_sum_slabs_kernel<T><<<grid, 256, 0, h->stream>>>(sp);
+    h->launches += 3;
+    CUDA_CHECK(cudaGetLastError());
     return 0;
 }
 
@@ -1326,6 +1387,12 @@ int hmb200_peer_allgather_range(hmb200_handle *h, const void *local_part, int64_
     return guarded([&] {
         if (!h || (!local_part && count > 0) || elem_offset < 0) throw std::runtime_error("null argument / negative offset");
         return h->es == 8 ? peer_allgather<double>(h, local_part, y_replicated, elem_offset, count) : peer_allgather<double2>(h, local_part, y_replicated, elem_offset, count);
+    });
+}
+int hmb200_peer_exchange_sum(hmb200_handle *h, char trans, const double *alpha, const void *x_local, const double *beta, void *y_local) {
+    return guarded([&] {
+        if (!h || !alpha || !beta || (h->n_rows > 0 && (!x_local || !y_local))) throw std::runtime_error("null argument");
+        return h->es == 8 ? peer_exchange_sum<double>(h, trans, alpha, x_local, beta, y_local) : peer_exchange_sum<double2>(h, trans, alpha, x_local, beta, y_local);
     });
 }
 int hmb200_peer_allreduce_f64(hmb200_handle *h, double *vals, int n) {

@@ -189,6 +189,7 @@ class B200DistributedOperator:
         self._peer_failed = 0
         self.split_input_upload = True  # `matvec` on several GPUs: each rank uploads 1/P of x, NVLink exchange (needs identical x on all ranks)
         self._ybuf = None
+        self._t_slab = None  # slab-sized device temporary of the transposed global product
         if fused_allgather is None:
             fused_allgather = self.world > 1
         if fused_allgather:
@@ -361,6 +362,28 @@ class B200DistributedOperator:
         _lib.check(_lib.lib().hmb200_peer_allreduce_f64(self.engine._h, t.data_ptr(), n))
         return t
 
+    def peer_exchange_sum_(self, x_local, y_local, trans: str = "T", alpha=1.0, beta=0.0):
+        """y_local = beta y_local + sum over the ranks (ascending) of the slab of alpha op(A_q) x_q, op = 'T' / 'C': every rank's
+        full-length contribution stays in its own peer-mapped buffer and the slabs are pulled over NVLink and added in rank
+        order by one kernel (hmb200_peer_exchange_sum) -- the MPI_Alltoallv + axpy loop of
+        add_distributed_operator_vector_product_local_to_local.hpp:60-87 without NCCL.  Collective."""
+        import ctypes
+
+        import torch
+
+        if not self.fused:
+            raise RuntimeError("fused all-gather is not set up on this operator")
+        if self._peer_failed:
+            self.check_peers()
+        eng, s = self.engine, self.sizes[self.rank]
+        eng.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+        px, _ = eng._ptr(x_local, s, False)
+        py, _ = eng._ptr(y_local, s, True)
+        a = (ctypes.c_double * 2)(complex(alpha).real, complex(alpha).imag)
+        b = (ctypes.c_double * 2)(complex(beta).real, complex(beta).imag)
+        _lib.check(_lib.lib().hmb200_peer_exchange_sum(eng._h, trans.encode(), a, px, b, py))
+        return y_local
+
     def peer_status(self, sync: bool = True) -> int:
         """0, or 1 + the rank whose epoch did not arrive within a wait kernel's bound (101 + rank: an all-reduce).  The word
         lives in mapped host memory; with sync=False it covers the waits that have already completed on the stream."""
@@ -399,6 +422,16 @@ class B200DistributedOperator:
         if trans not in ("T", "C"):
             raise ValueError("trans must be 'T' or 'C'")
         o, s = self.offs[self.rank], self.sizes[self.rank]
+        if self.world > 1 and self.fused and self.n_target == self.n_source:
+            # reduce-scatter (rank-ordered sums pulled over NVLink) + all-gather, both on the peer regions: no NCCL call, and
+            # every rank holds the same bits
+            import torch
+
+            if self._t_slab is None:
+                self._t_slab = torch.empty(s, dtype=self.torch_dtype, device=self.device)
+            self.peer_exchange_sum_(x_cluster[o:o + s], self._t_slab, trans, 1.0, 0.0)
+            y_cluster.copy_(self.peer_allgather_(self._t_slab))
+            return y_cluster
         self.engine.add_vector_product(trans, 1.0, x_cluster[o:o + s], 0.0, y_cluster)
         if self.world > 1:
             import torch
@@ -428,6 +461,8 @@ class B200DistributedOperator:
             return y_local
         if trans not in ("T", "C"):
             raise ValueError("trans must be 'N', 'T' or 'C'")
+        if self.fused:
+            return self.peer_exchange_sum_(x_local, y_local, trans, alpha, beta)
         full = self._buffers(1)[0][2]
         self.engine.add_vector_product(trans, alpha, x_local, 0.0, full)
         return exchange_sum_slabs_(full, self.offs, self.sizes, y_local, beta, self.group if torch.distributed.is_initialized() else None)

@@ -189,6 +189,12 @@ int hmb200_peer_allgather(hmb200_handle *h, const void *local_slab, void **y_rep
  * input that every rank holds on the host: each rank uploads 1/P of it and the chunks are exchanged over NVLink) */
 int hmb200_peer_allgather_range(hmb200_handle *h, const void *local_part, int64_t elem_offset, int64_t count, void **y_replicated);
 int hmb200_peer_allreduce_f64(hmb200_handle *h, double *vals, int n);
+/* the exchange of the TRANSPOSED local-to-local product on the same regions (trans = 'T' or 'C', needs build_transpose=1 and a
+ * square operator): y_local = beta y_local + sum over the ranks q, ascending, of [alpha op(A_q) x_q](slab of this rank).  Every
+ * rank leaves its full-length contribution in its own replicated buffer and pulls its slab of all contributions over NVLink --
+ * the MPI_Alltoallv + scal + one axpy per rank of ..._vector_product_local_to_local.hpp:60-87.  x_local / y_local: device, n_rows
+ * elements; alpha, beta as in hmb200_vector_product_*; collective, counts as one product of step 3. */
+int hmb200_peer_exchange_sum(hmb200_handle *h, char trans, const double *alpha, const void *x_local, const double *beta, void *y_local);
 int hmb200_vector_product_allgather_d(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated);
 int hmb200_vector_product_allgather_z(hmb200_handle *h, const double *alpha, const double *in, void **y_replicated);
 

@@ -296,6 +296,26 @@ def _dist_worker(rank, world, port, q, kernel="laplace_reg"):
                 fo.add_vector_product(f, tr, 1.0, np.ascontiguousarray(xt[offs[p]:offs[p] + sizes[p]]), 0.0, part)
                 yt_ref += part
             et = max(et, rel_err(yt.cpu().numpy(), yt_ref))
+            if world > 1:
+                # the same product on the peer regions (rank-ordered reduce-scatter pulled over NVLink + all-gather): no NCCL call,
+                # the same bits on every rank, repeated calls (alternating buffers) identical
+                if tr == "T":
+                    op_tp = B200DistributedOperator(slab, tree.partition, build_transpose=1)
+                same = same and op_tp.fused
+                outs = []
+                for _ in range(3):
+                    yp = torch.zeros(n, dtype=op_tp.torch_dtype, device=op_tp.device)
+                    op_tp.matvec_cluster_transposed_(torch.from_numpy(xt).to(op_tp.device), yp, tr)
+                    outs.append(yp)
+                    op_tp.matvec_cluster_fused_(torch.from_numpy(xt).to(op_tp.device))  # an 'N' product in between: shared epochs / buffers
+                et = max(et, rel_err(outs[0].cpu().numpy(), yt_ref))
+                same = same and all(torch.equal(o, outs[0]) for o in outs[1:])
+                mine = torch.view_as_real(outs[0]).contiguous() if outs[0].is_complex() else outs[0]
+                gathered = [torch.empty_like(mine) for _ in range(world)]
+                dist.all_gather(gathered, mine)
+                same = same and all(torch.equal(g, gathered[0]) for g in gathered[1:]) and op_tp.peer_status() == 0
+        if world > 1:
+            op_tp.close()
         op_t.close()
         # device GMRES on the distributed operator vs the oracle GMRES over the restated slabs
         from htool_python_b200 import B200Solver
@@ -362,25 +382,29 @@ def test_distributed_operator(world, kernel):
         assert it == it_ref and 0 < it < 100 and ex < 1e-7, (rank, it, it_ref, ex)
 
 
+@pytest.mark.parametrize("fused", [False, True])
 @pytest.mark.parametrize("name", ["d_N_cylinder", "z_N_sphere"])
-def test_local_to_local_driver_single_rank(name):
-    """matvec_local_to_local_ with one rank: 'N' and the transposed branches (alpha, beta) vs the oracle"""
+def test_local_to_local_driver_single_rank(name, fused):
+    """matvec_local_to_local_ with one rank: 'N' and the transposed branches (alpha, beta) vs the oracle; fused = on the peer
+    regions (input gather kernel / contribution published in place + slab sum kernel, epoch flags), else the NCCL-path code"""
     import torch
 
     from htool_python_b200 import B200DistributedOperator
 
     flat, _ = load_golden(name)
     n = flat.n_rows
-    op = B200DistributedOperator(flat, [(0, n)], fused_allgather=False, build_transpose=1)
+    op = B200DistributedOperator(flat, [(0, n)], fused_allgather=fused, build_transpose=1)
+    assert op.fused == fused
     rng = np.random.default_rng(0)
-    alpha, beta = (1.25, -0.5)
-    for tr in ["N", "T"] + (["C"] if flat.dtype == "z" else []):
-        x, y0 = helpers.rand_vec(rng, n, flat.np_dtype), helpers.rand_vec(rng, n, flat.np_dtype)
-        y = torch.from_numpy(y0.copy()).to(op.device)
-        op.matvec_local_to_local_(torch.from_numpy(x).to(op.device), y, tr, alpha, beta)
-        ref = y0.copy()
-        fo.add_vector_product(flat, tr, alpha, x, beta, ref)
-        assert rel_err(y.cpu().numpy(), ref) < TOL, tr
+    for alpha, beta in [(1.25, -0.5), (1.0, 0.0)] + ([(0.5 - 0.25j, 0.75 + 0.5j)] if flat.dtype == "z" else []):
+        for tr in ["N", "T"] + (["C"] if flat.dtype == "z" else []):
+            x, y0 = helpers.rand_vec(rng, n, flat.np_dtype), helpers.rand_vec(rng, n, flat.np_dtype)
+            y = torch.from_numpy(y0.copy()).to(op.device)
+            op.matvec_local_to_local_(torch.from_numpy(x).to(op.device), y, tr, alpha, beta)
+            ref = y0.copy()
+            fo.add_vector_product(flat, tr, alpha, x, beta, ref)
+            assert rel_err(y.cpu().numpy(), ref) < TOL, (tr, alpha, beta)
+    assert op.peer_status() == 0
     op.close()
 
 
@@ -424,7 +448,25 @@ def _l2l_worker(rank, world, port, q):
                     fo.add_vector_product(f, "T", 1.25, np.ascontiguousarray(xg[offs[p]:offs[p] + sizes[p]]), 0.0, part)
                     ref += part
             errs.append(rel_err(y_loc.cpu().numpy(), ref[offs[rank]:offs[rank] + sizes[rank]]))
+        # the transposed exchange on the peer regions: bit-identical to the NCCL leg for beta = 0 (same rank-ordered sum), and
+        # freely mixed with the 'N' driver (shared buffers and epochs)
+        opf = B200DistributedOperator(flats[rank], tree.partition, build_transpose=1)
+        assert opf.fused
+        x_loc = dev(xg[offs[rank]:offs[rank] + sizes[rank]])
+        for it in range(4):
+            y0 = rng.random(n)
+            beta = 0.0 if it % 2 == 0 else -0.5
+            ya, yb = dev(y0[offs[rank]:offs[rank] + sizes[rank]]), dev(y0[offs[rank]:offs[rank] + sizes[rank]])
+            op.matvec_local_to_local_(x_loc, ya, "T", 1.25, beta)
+            opf.matvec_local_to_local_(x_loc, yb, "T", 1.25, beta)
+            errs.append(0.0 if torch.equal(ya, yb) else max(1.0 if beta == 0.0 else 0.0, rel_err(yb.cpu().numpy(), ya.cpu().numpy())))
+            yn_a, yn_b = torch.zeros_like(ya), torch.zeros_like(ya)
+            op.matvec_local_to_local_(x_loc, yn_a, "N")
+            opf.matvec_local_to_local_(x_loc, yn_b, "N")
+            errs.append(0.0 if torch.equal(yn_a, yn_b) else 1.0)
+        errs.append(float(opf.peer_status()))
         q.put((rank, errs))
+        opf.close()
         op.close()
     finally:
         dist.destroy_process_group()
@@ -611,6 +653,35 @@ def test_device_products_replayed_from_cuda_graphs():
     y.copy_(y0)
     e.add_vector_product("N", 1.5, x, -0.25, y)
     assert np.array_equal(y.cpu().numpy(), outs[0])
+    e.close()
+
+
+def test_graph_cache_survives_many_distinct_buffers():
+    """more distinct (in, out) pairs than the graph cache holds: a solver's recurring pair keeps replaying bit-identically
+    while one-off and twice-used buffers stream past (the cache trims one-off keys first, then the least recently used)"""
+    import torch
+
+    rng = np.random.default_rng(17)
+    flat = synthetic_flat(rng, 300, 280, max_leaf=32)
+    e = _engine(flat)
+    x = torch.from_numpy(helpers.rand_vec(rng, 280, np.float64)).cuda()
+    y_ref = np.zeros(300)
+    fo.add_vector_product(flat, "N", 1.0, x.cpu().numpy(), 0.0, y_ref)
+    y_hot = torch.empty(300, dtype=torch.float64, device="cuda")
+    pool = torch.zeros(700, 304, dtype=torch.float64, device="cuda")
+    first = None
+    for k in range(700):
+        for _ in range(2 if k % 3 == 0 else 1):  # every third buffer gets a graph of its own
+            e.add_vector_product("N", 1.0, x, 0.0, pool[k, :300])
+        if k % 50 == 0:
+            e.add_vector_product("N", 1.0, x, 0.0, y_hot)
+            got = y_hot.cpu().numpy().copy()
+            first = got if first is None else first
+            assert np.array_equal(got, first)
+    torch.cuda.synchronize()
+    assert rel_err(first, y_ref) < TOL
+    out = pool[:, :300].cpu().numpy()
+    assert all(np.array_equal(out[k], first) for k in range(700))
     e.close()
 
 
