@@ -70,6 +70,8 @@ def parse():
     ap.add_argument("--no-gmres-regularised", action="store_true", help="with --gmres: skip the second solve on the reference's regularised test kernel")
     ap.add_argument("--transposed", action="store_true", help="also time y = A^T x (and A^H x for complex) on the same operator: adds a 'transposed' object "
                     "(packs the transposed streams too: twice the device memory)")
+    ap.add_argument("--transposed-exchange", choices=["nccl", "peer"], default="nccl", help="with --transposed at N > 1: NCCL all-reduce of the full-length "
+                    "contributions (default, measured faster) or the rank-ordered reduce-scatter + all-gather on the peer regions")
     ap.add_argument("--engine-opts", default="", help="k=v,k=v overrides of hmb200_options (tuning runs)")
     a = ap.parse_args()
     preset = CONFIGS.get(a.config or 1)
@@ -396,6 +398,8 @@ def run_b200(args):
     # ---- transposed / conjugate-transposed products (trans != 'N' of the operator interface) -----------------------------------
     tr_obj = None
     if args.transposed and mu == 1:
+        if world > 1:
+            op.transposed_exchange = args.transposed_exchange
         tr_obj = run_transposed(args, op, engine, H, flat, x_cluster_host, world, rank, dev, thr, barrier, max_over_ranks)
 
     # ---- GMRES with the Krylov basis resident on the device (BASELINE.json configs[4]) --------------------------------
@@ -546,7 +550,14 @@ def run_transposed(args, op, engine, H, flat, x_cluster_host, world, rank, dev, 
             getattr(ro, "internal_vector_product_addr_" + flat.dtype)(H.address, tr, 1.0, np.ascontiguousarray(x_cluster_host[o:o + s]), 0.0, ref, True)
             rec["parity_rel_err_vs_reference"] = max_over_ranks(np.linalg.norm(part.cpu().numpy() - ref) / np.linalg.norm(ref))
         out[tr] = rec
-    out["driver"] = "engine call (1 GPU)" if world == 1 else "op(A_p) x_p on every rank + NCCL all-reduce of the full-length results"
+    if world == 1:
+        out["driver"] = "engine call (1 GPU)"
+    elif getattr(op, "fused", False) and getattr(op, "transposed_exchange", "nccl") == "peer":
+        out["driver"] = ("op(A_p) x_p on every rank into its own peer-mapped buffer; rank-ordered slab sums pulled over NVLink "
+                         "(hmb200_peer_exchange_sum) + peer all-gather; no NCCL call")
+        out["peer_status"] = int(op.peer_status())
+    else:
+        out["driver"] = "op(A_p) x_p on every rank + NCCL all-reduce of the full-length results"
     return out
 
 

@@ -190,6 +190,10 @@ class B200DistributedOperator:
         self.split_input_upload = True  # `matvec` on several GPUs: each rank uploads 1/P of x, NVLink exchange (needs identical x on all ranks)
         self._ybuf = None
         self._t_slab = None  # slab-sized device temporary of the transposed global product
+        # `matvec_cluster_transposed_` at world > 1: "nccl" = one all-reduce of the full-length contributions (measured faster: 1.42
+        # vs 1.53 ms at N=1M on 2 GPUs, profiles/r02_bench_N1M_transposed.json); "peer" = rank-ordered reduce-scatter + all-gather
+        # on the peer regions (no NCCL call, the same bits on every rank and run)
+        self.transposed_exchange = "nccl"
         if fused_allgather is None:
             fused_allgather = self.world > 1
         if fused_allgather:
@@ -422,7 +426,7 @@ class B200DistributedOperator:
         if trans not in ("T", "C"):
             raise ValueError("trans must be 'T' or 'C'")
         o, s = self.offs[self.rank], self.sizes[self.rank]
-        if self.world > 1 and self.fused and self.n_target == self.n_source:
+        if self.world > 1 and self.fused and self.transposed_exchange == "peer" and self.n_target == self.n_source:
             # reduce-scatter (rank-ordered sums pulled over NVLink) + all-gather, both on the peer regions: no NCCL call, and
             # every rank holds the same bits
             import torch

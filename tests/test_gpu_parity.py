@@ -301,6 +301,7 @@ def _dist_worker(rank, world, port, q, kernel="laplace_reg"):
                 # the same bits on every rank, repeated calls (alternating buffers) identical
                 if tr == "T":
                     op_tp = B200DistributedOperator(slab, tree.partition, build_transpose=1)
+                    op_tp.transposed_exchange = "peer"
                 same = same and op_tp.fused
                 outs = []
                 for _ in range(3):
