@@ -76,6 +76,7 @@ EXPORTS = {
     "hmb200_krylov_combine": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_double, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p]),
     "hmb200_krylov_axpby": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p]),
     "hmb200_krylov_scale": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_void_p]),
+    "hmb200_krylov_dots_static": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_int, c_void_p]),
     "hmb200_last_kernel_ms": (c_int, [c_void_p, POINTER(c_float * 4)]),
     "hmb200_kernel_ms_avg": (c_int, [c_void_p, POINTER(c_float * 4), POINTER(c_int)]),
     "hmb200_enable_timing": (c_int, [c_void_p, c_int]),

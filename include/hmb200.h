@@ -232,6 +232,23 @@ int hmb200_krylov_dots(const void *V, int64_t ldv, int k, const void *w, int64_t
 int hmb200_krylov_combine(const void *V, int64_t ldv, int k, const void *h, double sign, void *w, int64_t n, double *norm2, void *scratch, int elem_bytes, void *stream);
 int hmb200_krylov_axpby(const double *alpha, const void *x, const double *beta, const void *y, void *out, int64_t n, double *norm2, void *scratch, int elem_bytes, void *stream);
 int hmb200_krylov_scale(void *w, int64_t n, const double *norm2, int elem_bytes, void *stream);
+/* hmb200_krylov_dots for callers that cannot bring a workspace.  (No counterpart in the reference: its solver runs on host
+ * vectors and never needs one.)  Some users of this library are not able to allocate device memory at the point where they
+ * need the dot products: an operator or orthogonalisation callback that a foreign solver calls with raw pointers only, code
+ * that was handed a stream it must not stall (cudaMalloc / cudaFree synchronise the whole device), a process whose HBM is
+ * fully planned in advance, or a C / Fortran / ctypes host with no device allocator.  This variant takes the same V, ldv, k,
+ * w, n, h as hmb200_krylov_dots and writes the same h (same kernels, same summation order), but keeps its partial sums in an
+ * array that is built into the library's device code, so neither the caller nor the library allocates anything.
+ *   Limit: ceil(n / 2048) * k * elem_bytes <= HMB200_STATIC_SCRATCH_BYTES (4 MiB: e.g. n = 1M rows with k <= 1072 real or
+ *     536 complex basis vectors).  Anything larger is refused with a non-zero status and a message; use hmb200_krylov_dots.
+ *   Cost: each GPU that loads the library's kernels keeps those 4 MiB until the process ends.
+ *   First call per device: looks up the array's address on the CURRENT device (the one V, w, h live on must be current).
+ *     Make that first call during set-up, before any stream capture.
+ *   Sharing: one array per GPU for all calls; it is not cleared between calls and does not need to be (every partial sum that
+ *     is read was written by the same call).  Calls that may overlap on one GPU (two streams, two threads) corrupt each
+ *     other's partial sums: issue them one after the other on one stream, or order them with events. */
+#define HMB200_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int hmb200_krylov_dots_static(const void *V, int64_t ldv, int k, const void *w, int64_t n, void *h, int elem_bytes, void *stream);
 
 /* timing of the kernels of the last product on the handle's stream (CUDA events), in milliseconds:
  * ms[0] phase 1 (t = V x), ms[1] partial reduce, ms[2] phase 2 (y += U t, y += D x), ms[3] whole product */
