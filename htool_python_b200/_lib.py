@@ -53,6 +53,7 @@ EXPORTS = {
     "hmb200_matmat_user_chunked_z": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int]),
     "hmb200_peer_mm_create": (c_int, [c_void_p, c_int, c_void_p]),
     "hmb200_peer_mm_attach": (c_int, [c_void_p, c_void_p]),
+    "hmb200_peer_mm_detach": (c_int, [c_void_p]),
     "hmb200_peer_mm_buffer": (c_int, [c_void_p, c_int, POINTER(c_void_p)]),
     "hmb200_matrix_product_allgather_d": (c_int, [c_void_p, c_void_p, c_void_p, c_int, POINTER(c_void_p)]),
     "hmb200_matrix_product_allgather_z": (c_int, [c_void_p, c_void_p, c_void_p, c_int, POINTER(c_void_p)]),

@@ -1290,10 +1290,16 @@ int hmb200_peer_mm_create(hmb200_handle *h, int mu, unsigned char *ipc_handle_ou
         if (mu < 1) throw std::runtime_error("mu must be positive");
         CUDA_CHECK(cudaSetDevice(h->device));
         CUDA_CHECK(cudaStreamSynchronize(h->stream));
-        for (int q = 0; q < pr.n_ranks; q++) { // a previous set of blocks (another mu) is released first
-            if (!pr.mm_region[q]) continue;
-            if (q == pr.rank) CUDA_CHECK(cudaFree(pr.mm_region[q])); else CUDA_CHECK(cudaIpcCloseMemHandle(pr.mm_region[q]));
-            pr.mm_region[q] = nullptr;
+        // A previous set of blocks (another mu) is released first.  Freeing an exported region that a peer still has open is
+        // undefined, and a peer may still be storing into it: the owner frees only after EVERY rank has run
+        // hmb200_peer_mm_detach (stream drained, imports closed) and the ranks have met at a barrier -- this rank's own
+        // imports being closed is the part of that protocol that can be checked here.
+        for (int q = 0; q < pr.n_ranks; q++)
+            if (q != pr.rank && pr.mm_region[q])
+                throw std::runtime_error("multi-RHS peer blocks of another width are still attached: call hmb200_peer_mm_detach on every rank, then synchronise the ranks, before hmb200_peer_mm_create");
+        if (pr.mm_region[pr.rank]) {
+            CUDA_CHECK(cudaFree(pr.mm_region[pr.rank]));
+            pr.mm_region[pr.rank] = nullptr;
         }
         pr.mm_attached  = false;
         pr.mm_mu        = mu;
@@ -1305,6 +1311,22 @@ int hmb200_peer_mm_create(hmb200_handle *h, int mu, unsigned char *ipc_handle_ou
         cudaIpcMemHandle_t ih;
         CUDA_CHECK(cudaIpcGetMemHandle(&ih, r));
         std::memcpy(ipc_handle_out, &ih, 64);
+        return 0;
+    });
+}
+int hmb200_peer_mm_detach(hmb200_handle *h) {
+    return guarded([&] {
+        if (!h) throw std::runtime_error("null handle");
+        hmb200_handle::Peer &pr = h->peer;
+        CUDA_CHECK(cudaSetDevice(h->device));
+        CUDA_CHECK(cudaStreamSynchronize(h->stream)); // this rank's stores into the peers' blocks have landed
+        pr.mm_attached = false;
+        for (int q = 0; q < pr.n_ranks; q++) {
+            if (q == pr.rank || !pr.mm_region[q]) continue;
+            uint8_t *m      = pr.mm_region[q];
+            pr.mm_region[q] = nullptr;
+            CUDA_CHECK(cudaIpcCloseMemHandle(m));
+        }
         return 0;
     });
 }

@@ -478,6 +478,17 @@ class B200DistributedOperator:
         import torch.distributed as dist
 
         lib = _lib.lib()
+        if getattr(self, "_mm_mu", 0):
+            # another width: no owner may free its blocks while a peer still stores into them or has them open, so every rank
+            # drains its stream and closes its imports first, and the ranks meet before anyone re-creates (the exchange of the
+            # status is that barrier).  Views handed out for the old width (matmat_cluster_fused_) are dead from here on.
+            self._mm_ybuf, self._mm_mu = {}, 0
+            ok = lib.hmb200_peer_mm_detach(self.engine._h) == 0
+            err = "" if ok else _lib.last_error()
+            oks = [None] * self.world
+            dist.all_gather_object(oks, ok, group=self.group)
+            if not all(oks):
+                raise RuntimeError(f"hmb200: the replicated multi-RHS blocks of the previous width could not be released ({err or 'a peer failed'})")
         handle = (ctypes.c_ubyte * 64)()
         ok = lib.hmb200_peer_mm_create(self.engine._h, int(mu), handle) == 0
         err = "" if ok else _lib.last_error()
@@ -504,7 +515,8 @@ class B200DistributedOperator:
     def matmat_cluster_fused_(self, X_cluster, mu: int):
         """returns the replicated Y = A X (row-major n_target x mu, cluster numbering) as a view of one of the operator's two
         peer-mapped blocks: the multi-RHS slab product stores every bin's rows into the block of every rank from its epilogue
-        (no NCCL call).  Collective; the returned tensor stays valid until the product after the next."""
+        (no NCCL call).  Collective; the returned tensor stays valid until the product after the next -- or until a product with
+        another `mu`, which releases and re-creates the blocks on every rank."""
         import ctypes
 
         if not self.fused:
@@ -772,7 +784,9 @@ class B200DistributedOperator:
         """`A @ X` for a Fortran-ordered (n_source, mu) host block in user numbering.  On several ranks of one node (peer regions
         set up, square operator) every rank uploads its 1/P of the ROWS of X and downloads its 1/P of the rows of Y
         (hmb200_matmat_user_chunked_*); the result lands in a node-shared page-locked block that `out="shared"` returns without
-        a copy (valid until the call after the next).  Page-locked X is DMA'd directly, pageable X goes through a pinned chunk."""
+        a copy (valid until the call after the next, or until a call with another number of columns: that releases the shared block
+        and the peer-mapped device blocks on every rank, so copy what must outlive it).  Page-locked X is DMA'd directly, pageable X
+        goes through a pinned chunk."""
         import time
 
         import torch

@@ -153,8 +153,13 @@ int hmb200_peer_status(hmb200_handle *h, int *err);
  * mu: the old blocks are released), exchange the handles, hmb200_peer_mm_attach; then, collectively,
  * hmb200_matrix_product_allgather_{d,z}(h, alpha, in (device, n_cols x mu row-major), mu, &Y): Y (device pointer into this
  * rank's region, n_global x mu row-major, cluster numbering) = alpha * A * in on all ranks -- the bin epilogue of the multi-RHS
- * kernel stores every tile row to all ranks, same epoch flags; counts as one collective of the sequence above. */
+ * kernel stores every tile row to all ranks, same epoch flags; counts as one collective of the sequence above.
+ * Changing mu is a two-phase collective: (1) every rank calls hmb200_peer_mm_detach (drains its stream, closes the blocks it
+ * imported from its peers); (2) the ranks synchronise (any barrier); (3) every rank calls hmb200_peer_mm_create for the new mu --
+ * only then does an owner free its old blocks -- and the handles are exchanged and attached as before.  hmb200_peer_mm_create
+ * refuses to run while this rank still has blocks of its peers attached.  Pointers returned for the old mu are dead after (1). */
 int hmb200_peer_mm_create(hmb200_handle *h, int mu, unsigned char *ipc_handle_out);
+int hmb200_peer_mm_detach(hmb200_handle *h);
 int hmb200_peer_mm_attach(hmb200_handle *h, const unsigned char *ipc_handles);
 int hmb200_peer_mm_buffer(hmb200_handle *h, int index, void **ptr);
 int hmb200_matrix_product_allgather_d(hmb200_handle *h, const double *alpha, const double *in, int mu, void **y_replicated);
