@@ -83,6 +83,8 @@ EXPORTS = {
     "hmb200_enable_timing": (c_int, [c_void_p, c_int]),
     "hmb200_launch_count": (c_int64, [c_void_p]),
     "hmb200_fp64_rate": (c_int, [c_int, POINTER(c_double), POINTER(c_double)]),
+    "hmb200_host_flag_publish": (c_int, [c_void_p, c_int64]),
+    "hmb200_host_flags_wait": (c_int, [c_void_p, c_int64, c_int, c_int64, c_double, POINTER(c_int)]),
     "hmb200_last_error": (c_char_p, []),
     "hmb200_version": (c_char_p, []),
 }

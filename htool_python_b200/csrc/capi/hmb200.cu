@@ -124,6 +124,7 @@ struct hmb200_handle {
     size_t pinned_bytes = 0;
     uint32_t *counters = nullptr; // [2]
     int32_t *perm_t = nullptr, *perm_s = nullptr;
+    int64_t gperm_n_target = 0;                    // n_target of the first hmb200_set_global_permutations call (sizes ginv_t, gy)
     int32_t *gperm_s = nullptr, *ginv_t = nullptr; // distributed user-numbering product: full source permutation, inverse target permutation
     void *gx = nullptr, *gy = nullptr;             // ... and its chunk staging (n_global elements each, never reallocated: cached graphs hold them)
     // per-kernel timing: a ring of CUDA-event quads recorded on the launching stream, collected lazily (no sync in the
@@ -584,8 +585,11 @@ void run_cached(hmb200_handle *h, const hmb200_handle::GraphKey &key, F &&issue)
     if (h->graphs.size() > hmb200_handle::kMaxGraphKeys && !h->graphs.count(key)) trim_graphs(h);
     auto &ge = h->graphs[key];
     ge.last_use = ++h->graph_tick;
-    if (!ge.exec && ++ge.seen < 2 && key.fused == 0) {
-        issue(); // first use of a key runs eagerly (one-off pointers never pay for a capture); fused products always recur
+    // first use of a key runs eagerly (one-off pointers never pay for a capture).  Fused device-resident products always recur
+    // (the operator's own two buffers); the chunked host product ('U') is keyed on the CALLER's host pointers, which may well be
+    // one-off, so it waits for the second sight like everything else.
+    if (!ge.exec && ++ge.seen < 2 && (key.fused == 0 || key.op == 'U')) {
+        issue();
         return;
     }
     if (!ge.exec) {
@@ -1364,6 +1368,10 @@ int hmb200_set_global_permutations(hmb200_handle *h, const int32_t *source_perm,
     return guarded([&] {
         if (!h || !source_perm || !inverse_target_perm) throw std::runtime_error("null argument");
         if (n_source != h->n_cols || n_target < h->n_rows) throw std::runtime_error("permutation sizes do not match the operator");
+        // the buffers below are sized by the first call: a later call must bring the same sizes (a larger n_target would
+        // overrun ginv_t / gy)
+        if (h->ginv_t && n_target != h->gperm_n_target) throw std::runtime_error("hmb200_set_global_permutations was called before with another target size");
+        h->gperm_n_target = n_target;
         CUDA_CHECK(cudaSetDevice(h->device));
         if (!h->gperm_s) CUDA_CHECK(cudaMalloc(&h->gperm_s, sizeof(int32_t) * (size_t)std::max<int64_t>(n_source, 1)));
         if (!h->ginv_t) CUDA_CHECK(cudaMalloc(&h->ginv_t, sizeof(int32_t) * (size_t)std::max<int64_t>(n_target, 1)));

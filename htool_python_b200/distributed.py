@@ -98,6 +98,28 @@ def exchange_sum_slabs_(full, offs: List[int], sizes: List[int], out_local, beta
     return out_local
 
 
+def _nvml_handle_of_cuda_device(pynvml, index: int):
+    """NVML handle of CUDA device `index`.  NVML numbers ALL physical GPUs in PCI order and knows nothing of CUDA_VISIBLE_DEVICES /
+    CUDA_DEVICE_ORDER, so the CUDA index is only an NVML index on a full, unreordered allocation: match by UUID, and fall back to
+    the index only when no device mask is set.  Raises when the device cannot be identified (the caller then pins nothing, which
+    is better than pinning to the cores of another GPU's NUMA node)."""
+    import os
+
+    import torch
+
+    try:
+        uuid = str(torch.cuda.get_device_properties(index).uuid)
+        uuid = uuid if uuid.startswith(("GPU-", "MIG-")) else "GPU-" + uuid
+        try:
+            return pynvml.nvmlDeviceGetHandleByUUID(uuid)
+        except TypeError:
+            return pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+    except Exception:
+        if os.environ.get("CUDA_VISIBLE_DEVICES") or os.environ.get("CUDA_DEVICE_ORDER"):
+            raise
+        return pynvml.nvmlDeviceGetHandleByIndex(index)
+
+
 def bind_to_gpu_cpus(local_rank: int, local_world: int) -> list:
     """Pins this process to its share of the host cores next to GPU `local_rank` (NVML's ideal CPU set of the device, split
     between the ranks whose GPUs report the same set) -- what `mpirun --bind-to` does for the reference's ranks.  One process
@@ -113,7 +135,7 @@ def bind_to_gpu_cpus(local_rank: int, local_world: int) -> list:
         words = (max(allowed) // 64) + 1
         sets = []
         for g in range(local_world):
-            mask = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(g), words)
+            mask = pynvml.nvmlDeviceGetCpuAffinity(_nvml_handle_of_cuda_device(pynvml, g), words)
             sets.append(tuple(c for c in allowed if (mask[c // 64] >> (c % 64)) & 1))
         mine = sets[local_rank]
         if not mine:
@@ -254,7 +276,7 @@ class B200DistributedOperator:
         self._shm = None
         buf_bytes = (self.n_target * self.es + 4095) // 4096 * 4096
         nbytes = 4096 + 2 * buf_bytes
-        name = [None]
+        name, shm, base = [None], None, None
         if self.rank == 0:
             try:
                 shm = shared_memory.SharedMemory(create=True, size=nbytes)
@@ -279,9 +301,17 @@ class B200DistributedOperator:
                 ok = int(torch.cuda.cudart().cudaHostRegister(base.ctypes.data, nbytes, 0)) == 0
         oks = [None] * self.world
         dist.all_gather_object(oks, bool(ok), group=self.group)
-        if not all(oks):
+        if not all(oks):  # a rank could not attach or page-lock: nobody keeps the segment (rank 0 removes the name)
             if ok:
                 torch.cuda.cudart().cudaHostUnregister(base.ctypes.data)
+            base = None  # a live view would make close() raise BufferError
+            if shm is not None:
+                try:
+                    shm.close()
+                    if self.rank == 0:
+                        shm.unlink()
+                except Exception as e:
+                    warnings.warn(f"hmb200: could not release the shared result segment ({e})")
             return
         self._shm, self._shm_base, self._shm_calls = shm, base, 0
         self._shm_flags = np.frombuffer(shm.buf, dtype=np.int64, count=512)[::8][:self.world]  # one 64-byte line per rank
@@ -632,8 +662,6 @@ class B200DistributedOperator:
         """the distributed user-numbering product as ONE library call per rank (one cached CUDA graph: H2D of this rank's 1/P
         chunk of x, all-gather of the chunks over NVLink, permutation, slab product with the fused all-gather, permutation of this
         rank's 1/P chunk of y, D2H into the node-shared page-locked result vector), then the host-side flags."""
-        import time
-
         k = self._shm_calls
         self._shm_calls += 1
         b = k & 1
@@ -650,12 +678,7 @@ class B200DistributedOperator:
         if st != 0:
             self._peer_failed = self._peer_failed or self.peer_status(sync=False) or 1
             _lib.check(st)
-        fl = self._shm_flags
-        fl[self.rank] = k + 1
-        t0 = time.perf_counter()
-        while int(fl.min()) < k + 1:
-            if time.perf_counter() - t0 > self.shared_result_timeout_s:
-                raise RuntimeError(f"hmb200: rank {int(fl.argmin())} did not deliver its chunk of the result within {self.shared_result_timeout_s} s")
+        self._publish_and_wait(self._shm_flags, k + 1)
         if isinstance(out, str):
             return res
         if out is None:
@@ -667,8 +690,6 @@ class B200DistributedOperator:
         """root_cluster_to_global of THIS rank's 1/P chunk of the user-numbered result, one D2H copy of that chunk into the
         node-shared page-locked buffer, host-side flag, wait for the other ranks' flags.  Two result buffers alternate: a
         rank can be at most one call ahead of the others, so a returned vector stays intact until the call after the next."""
-        import time
-
         import torch
 
         k = self._shm_calls
@@ -680,12 +701,7 @@ class B200DistributedOperator:
         self._shm_y_t[b][c0:c1].copy_(yu[c0:c1], non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         self.check_peers()
-        fl = self._shm_flags
-        fl[self.rank] = k + 1
-        t0 = time.perf_counter()
-        while int(fl.min()) < k + 1:
-            if time.perf_counter() - t0 > self.shared_result_timeout_s:
-                raise RuntimeError(f"hmb200: rank {int(fl.argmin())} did not deliver its chunk of the result within {self.shared_result_timeout_s} s")
+        self._publish_and_wait(self._shm_flags, k + 1)
         res = self._shm_y[b]
         if isinstance(out, str):  # out="shared": the node-shared buffer itself (valid until the call after the next)
             return res
@@ -693,6 +709,19 @@ class B200DistributedOperator:
             return res.copy()
         np.copyto(out, res)
         return out
+
+    def _publish_and_wait(self, fl, value):
+        """this rank's part of the shared result is in place: publish `value` in its flag word (release store) and wait until every
+        rank has done the same (acquire loads with back-off, in C with the GIL released: hmb200_host_flag_publish / _flags_wait)"""
+        import ctypes
+
+        lib = _lib.lib()
+        stride = fl.strides[0] // 8
+        lib.hmb200_host_flag_publish(fl.ctypes.data + fl.strides[0] * self.rank, int(value))
+        laggard = ctypes.c_int(-1)
+        st = lib.hmb200_host_flags_wait(fl.ctypes.data, stride, len(fl), int(value), float(self.shared_result_timeout_s), ctypes.byref(laggard))
+        if st != 0:
+            raise RuntimeError(f"hmb200: rank {laggard.value} did not deliver its part of the result within {self.shared_result_timeout_s} s")
 
     def _as_pinned_tensor(self, a):
         """torch view of a page-locked, contiguous numpy array of the operator's dtype (None otherwise)"""
@@ -748,6 +777,7 @@ class B200DistributedOperator:
         if not all(oks):
             if ok:
                 torch.cuda.cudart().cudaHostUnregister(base.ctypes.data)
+            base = None  # a live view would make close() raise BufferError
             if shm is not None:
                 shm.close()
                 if self.rank == 0:
@@ -787,8 +817,6 @@ class B200DistributedOperator:
         a copy (valid until the call after the next, or until a call with another number of columns: that releases the shared block
         and the peer-mapped device blocks on every rank, so copy what must outlive it).  Page-locked X is DMA'd directly, pageable X
         goes through a pinned chunk."""
-        import time
-
         import torch
 
         X = np.asarray(X)
@@ -833,12 +861,7 @@ class B200DistributedOperator:
         if st != 0:
             self._peer_failed = self._peer_failed or self.peer_status(sync=False) or 1
             _lib.check(st)
-        fl = blk["flags"]
-        fl[self.rank] = k + 1
-        t0 = time.perf_counter()
-        while int(fl.min()) < k + 1:
-            if time.perf_counter() - t0 > self.shared_result_timeout_s:
-                raise RuntimeError(f"hmb200: rank {int(fl.argmin())} did not deliver its rows of the result within {self.shared_result_timeout_s} s")
+        self._publish_and_wait(blk["flags"], k + 1)
         if isinstance(out, str):
             return Y
         if out is None:

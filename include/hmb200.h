@@ -276,6 +276,14 @@ int hmb200_rows_to_block(const int32_t *perm, int n, int mu, const void *src_row
  * counterpart: bench.py reports them next to the achieved rate). */
 int hmb200_fp64_rate(int device, double *dmma_tflops, double *dfma_tflops);
 
+/* Host-side completion flags of the chunked user-numbering products (no reference counterpart: the reference's ranks meet in
+ * MPI_Allgatherv).  Every rank owns one int64 word of a node-shared segment (word q at flags + q*stride) and, after its part of
+ * the result has landed in the shared block, publishes the call counter there with release semantics; _wait returns 0 once
+ * all n words are >= value (acquire loads; spins briefly, then yields, then sleeps in 50 us steps), 2 after timeout_s seconds
+ * with *laggard = the first rank still behind.  Host code only: usable without a GPU. */
+int hmb200_host_flag_publish(int64_t *flag, int64_t value);
+int hmb200_host_flags_wait(const int64_t *flags, int64_t stride, int n, int64_t value, double timeout_s, int *laggard);
+
 const char *hmb200_last_error(void);
 const char *hmb200_version(void);
 

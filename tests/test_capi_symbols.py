@@ -49,3 +49,24 @@ def test_no_cpu_fallback_without_gpu():
         Engine(flat)
     with pytest.raises(RuntimeError, match="no CUDA device"):
         Engine(flat, device=0)
+
+
+def test_host_flags_publish_and_wait():
+    """hmb200_host_flag_publish / hmb200_host_flags_wait (host code only): strided words, a late publisher, the timeout"""
+    import threading
+    import time
+
+    lib = _lib.lib()
+    words = np.zeros(4 * 8, np.int64)
+    fl = words[::8]  # one 64-byte line per rank, as the operator lays them out
+    for q in (0, 1, 3):
+        assert lib.hmb200_host_flag_publish(fl.ctypes.data + fl.strides[0] * q, 5) == 0
+    assert list(fl) == [5, 5, 0, 5]
+    laggard = ctypes.c_int(-1)
+    t0 = time.perf_counter()
+    assert lib.hmb200_host_flags_wait(fl.ctypes.data, 8, 4, 5, 0.05, ctypes.byref(laggard)) == 2
+    assert laggard.value == 2 and 0.04 < time.perf_counter() - t0 < 2.0
+    assert "rank 2" in _lib.last_error()
+    threading.Timer(0.05, lambda: lib.hmb200_host_flag_publish(fl.ctypes.data + fl.strides[0] * 2, 6)).start()
+    assert lib.hmb200_host_flags_wait(fl.ctypes.data, 8, 4, 5, 10.0, ctypes.byref(laggard)) == 0  # >= value counts
+    assert lib.hmb200_host_flags_wait(fl.ctypes.data, 8, 0, 5, 0.0, None) == 0
