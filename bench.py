@@ -42,8 +42,10 @@ import numpy as np  # noqa: E402
 
 UNIT = "matvecs/s"
 WORKLOADS = {"laplace": "Laplace 1/(4 pi r), double,", "helmholtz": "Helmholtz exp(ikr)/(4 pi r), complex<double>,",
-             "laplace_reg": "regularised Laplace 1/(1e-5 + 4 pi r) (the reference's GeneratorTestDoubleSymmetric), double,"}
-CONFIGS = {1: dict(kernel="laplace", n=1_000_000, rhs=1), 2: dict(kernel="helmholtz", n=500_000, rhs=1),
+             "laplace_reg": "regularised Laplace 1/(1e-5 + 4 pi r) (the reference's GeneratorTestDoubleSymmetric), double,",
+             "invdist_reg": "1/(1e-1 + |x-y|) (the generator of the reference's example/use_hmatrix.py, example/define_generators.py:15-17), double,"}
+GEOMETRIES = {"sphere": "points on the unit sphere surface (seed 0)", "cylinder": "points on a cylinder of radius 1 and height 4 (theta, z uniform, seed 0)"}
+CONFIGS = {0: dict(kernel="invdist_reg", n=20_000, rhs=1, geometry="cylinder", symmetry="S"), 1: dict(kernel="laplace", n=1_000_000, rhs=1), 2: dict(kernel="helmholtz", n=500_000, rhs=1),
            3: dict(kernel="laplace", n=1_000_000, rhs=64), 4: dict(kernel="laplace", n=2_000_000, rhs=1, gmres=True)}
 
 
@@ -53,12 +55,15 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--config", type=int, default=0, choices=[0, 1, 2, 3, 4], help="BASELINE.json configs[c]; sets --kernel/--n/--rhs/--gmres")
+    ap.add_argument("--config", type=int, default=1, choices=[0, 1, 2, 3, 4], help="BASELINE.json configs[c]; sets --kernel/--n/--rhs/--gmres "
+                    "(0: the reference's CPU-runnable use_hmatrix.py case, N=20k on a cylinder, symmetric 'S','L'; sweep --leaf 10/64/128)")
+    ap.add_argument("--symmetry", default=None, choices=["N", "S"], help="symmetry given to the reference's HMatrixTreeBuilder ('S' stores the lower "
+                    "triangle, UPLO 'L'); default: what the config's reference example uses")
     ap.add_argument("--n", type=int, default=None)
     ap.add_argument("--eps", type=float, default=1e-3)
     ap.add_argument("--eta", type=float, default=10.0)
     ap.add_argument("--leaf", type=int, default=64)
-    ap.add_argument("--kernel", default=None, choices=["laplace", "helmholtz", "laplace_reg"])
+    ap.add_argument("--kernel", default=None, choices=["laplace", "helmholtz", "laplace_reg", "invdist_reg"])
     ap.add_argument("--wavenumber", type=float, default=0.0, help="helmholtz: k (default: 10 points per wavelength)")
     ap.add_argument("--rhs", type=int, default=None, help="right-hand sides per step (64 = BASELINE.json configs[3], multi-RHS tensor-core path)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -74,7 +79,12 @@ def parse():
                     "contributions (default, measured faster) or the rank-ordered reduce-scatter + all-gather on the peer regions")
     ap.add_argument("--engine-opts", default="", help="k=v,k=v overrides of hmb200_options (tuning runs)")
     a = ap.parse_args()
-    preset = CONFIGS.get(a.config or 1)
+    preset = CONFIGS[a.config]
+    a.geometry = preset.get("geometry", "sphere")
+    if a.symmetry is None:
+        a.symmetry = preset.get("symmetry", "N")
+    if a.symmetry != "N" and a.gpus > 1:
+        raise SystemExit("bench.py: --symmetry S is a single-GPU case (the block-row slabs of the distributed product are assembled 'N')")
     if a.kernel is None:
         a.kernel = preset["kernel"]
     if a.n is None:
@@ -89,24 +99,29 @@ def parse():
 def config_index(args, mu):
     if args.kernel == "helmholtz":
         return 2
+    if args.kernel == "invdist_reg":
+        return 0
     if mu > 1:
         return 3
     return 4 if (args.gmres and args.n >= 2_000_000) else 1
 
 
 def metric_name(args, mu):
-    kind = {"laplace": "Laplace 1/r, double", "helmholtz": "Helmholtz exp(ikr)/r, complex<double>", "laplace_reg": "regularised Laplace, double"}[args.kernel]
+    kind = {"laplace": "Laplace 1/r, double", "helmholtz": "Helmholtz exp(ikr)/r, complex<double>", "laplace_reg": "regularised Laplace, double", "invdist_reg": "1/(0.1+|x-y|) on a cylinder, double"}[args.kernel]
     n = f"{args.n // 1_000_000}M" if args.n % 1_000_000 == 0 else (f"{args.n // 1000}k" if args.n % 1000 == 0 else str(args.n))
     return f"H-matvecs/sec (N={n} {kind}, {'single RHS' if mu == 1 else str(mu) + ' RHS per product'})"
 
 
 def workload_name(args, n, mu):
-    return (f"{WORKLOADS[args.kernel]} H-matrix, N={n} points on the unit sphere surface (seed 0), eps={args.eps}, eta={args.eta}, "
+    return (f"{WORKLOADS[args.kernel]} H-matrix{' (symmetric, lower triangle stored)' if getattr(args, 'symmetry', 'N') == 'S' else ''}, N={n} {GEOMETRIES[getattr(args, 'geometry', 'sphere')]}, eps={args.eps}, eta={args.eta}, "
             f"leaf {args.leaf}, {'single-RHS matvec' if mu == 1 else str(mu) + '-RHS matmat (FP64 tensor-core path)'} (BASELINE.json configs[{config_index(args, mu)}])")
 
 
 def config_of(args, mu):
     """the workload description -- IDENTICAL on both arms (engine-only facts go under `impl_config`)"""
+    if args.kernel == "invdist_reg" and args.n <= 100_000:  # configs[0]: ~70 MB of factors would sit in the 126 MB L2 from step to step
+        return {"workload": workload_name(args, args.n, mu), "rhs_per_step": mu,
+                "l2": "operator smaller than L2: a 512 MB buffer is overwritten before every timed step (outside the per-step events), steps timed one by one; the e2e loop is not flushed"}
     return {"workload": workload_name(args, args.n, mu), "rhs_per_step": mu,
             "l2": "inputs larger than L2 (factor stream >> 126 MB, read once per step)"}
 
@@ -116,6 +131,14 @@ def sphere_points(n, seed=0):
     g = np.random.default_rng(seed).standard_normal((3, n))
     g /= np.linalg.norm(g, axis=0)
     return np.asfortranarray(g)
+
+
+def cylinder_points(n, seed=0):
+    """N points on a cylinder: x = cos(theta), y = sin(theta), z ~ U(0, 4) (the shape of the reference's
+    example/create_geometry.py without its clustering of the points)."""
+    rng = np.random.default_rng(seed)
+    theta, z = rng.random(n) * 2 * np.pi, rng.random(n) * 4.0
+    return np.asfortranarray(np.stack([np.cos(theta), np.sin(theta), z]))
 
 
 def host_threads(world):
@@ -131,7 +154,8 @@ def assemble(args, world, rank, log, kernel=None):
     from htool_python_b200 import FlatHMatrix, bridge
 
     t0 = time.time()
-    pts = sphere_points(args.n)
+    pts = cylinder_points(args.n) if getattr(args, "geometry", "sphere") == "cylinder" else sphere_points(args.n)
+    sym = getattr(args, "symmetry", "N")
     tree = bridge.create_cluster_tree(pts, 2, world, args.leaf)
     t1 = time.time()
     slab = rank if world > 1 else -1
@@ -143,7 +167,7 @@ def assemble(args, world, rank, log, kernel=None):
     depth += 1 if depth else 0  # the builder's depth test is off by one against size = n / 2^depth (measured)
     kernel = kernel or getattr(args, "kernel", "laplace")
     k = getattr(args, "wavenumber", 0.0) or 2 * np.pi * np.sqrt(args.n / (4 * np.pi)) / 10.0  # ~10 points per wavelength
-    H = bridge.build_hmatrix(kernel, tree, epsilon=args.eps, eta=args.eta, target_partition_number=slab, wavenumber=k,
+    H = bridge.build_hmatrix(kernel, tree, epsilon=args.eps, eta=args.eta, symmetry=sym, UPLO="L" if sym != "N" else "N", target_partition_number=slab, wavenumber=k,
                              partition_number_for_symmetry=slab, minimal_target_depth=depth, minimal_source_depth=depth)
     t2 = time.time()
     flat = FlatHMatrix.from_htool(H)
@@ -337,9 +361,23 @@ def run_b200(args):
             y_pin = torch.zeros(n, dtype=tdt).pin_memory().numpy()
             apply_user = lambda: op.matvec(x_pin, out=y_pin)  # noqa: E731
 
+    flush_buf = torch.empty(512 << 20, dtype=torch.uint8, device=dev) if config_of(args, mu)["l2"].startswith("operator smaller") else None
+
     def timed_region(steps):
         """`steps` products between two events on the launching stream; returns (ms per step as the max over ranks, host window)"""
         barrier()
+        if flush_buf is not None:  # small operator: evict it from L2 before every step, one event pair per step
+            t_a = time.perf_counter()
+            pairs = []
+            for _ in range(steps):
+                flush_buf.fill_(1)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                step()
+                e1.record()
+                pairs.append((e0, e1))
+            barrier()
+            return max_over_ranks(sum(a.elapsed_time(b) for a, b in pairs)) / steps, (t_a, time.perf_counter())
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t_a = time.perf_counter()
         ev0.record()
@@ -366,6 +404,8 @@ def run_b200(args):
     # (the timed region above replays CUDA graphs, which carry no per-kernel events)
     engine.enable_timing(True)
     for _ in range(args.steps):
+        if flush_buf is not None:
+            flush_buf.fill_(1)
         step()
     barrier()
     kms = engine.kernel_ms_avg()
