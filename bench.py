@@ -67,6 +67,9 @@ def parse():
     ap.add_argument("--wavenumber", type=float, default=0.0, help="helmholtz: k (default: 10 points per wavelength)")
     ap.add_argument("--rhs", type=int, default=None, help="right-hand sides per step (64 = BASELINE.json configs[3], multi-RHS tensor-core path)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--also-rhs", type=int, default=64, help="single-RHS runs on the Laplace / Helmholtz configs: also time and check ONE more workload on the "
+                    "operator already assembled -- blocks of this many right-hand sides (BASELINE.json configs[3]: device value, e2e through matmat, "
+                    "per-rank parity against the reference) -- reported under 'also' (0: skip)")
     ap.add_argument("--sustained-steps", type=int, default=400, help="steps of the sustained region reported next to the burst value (0: skip)")
     ap.add_argument("--gmres", action="store_true", help="also solve A x = b with the device-resident GMRES (BASELINE.json configs[4]; adds a 'gmres' object)")
     ap.add_argument("--gmres-block", type=int, default=0, help="with --gmres: also solve a block of this many right-hand sides in lockstep "
@@ -506,6 +509,11 @@ def run_b200(args):
         dist.all_gather_object(hs, (hashlib.blake2b(y_dev_host.tobytes(), digest_size=8).hexdigest(), hashlib.blake2b(y_user.tobytes(), digest_size=8).hexdigest()))
         replicas_identical = len(set(hs)) == 1
 
+    # ---- one more workload on the same operator: blocks of right-hand sides (BASELINE.json configs[3]) ---------------------------------
+    also = None
+    if mu == 1 and args.also_rhs > 1 and not args.no_cpu_baseline and args.kernel in ("laplace", "helmholtz") and info["mm_stream_bytes"] > 0:
+        also = {f"rhs{args.also_rhs}": run_also_rhs(args, args.also_rhs, op, engine, H, flat, x_user, world, rank, dev, thr, dmma_tf, w_all, log, barrier, max_over_ranks)}
+
     if rank == 0:
         h2d = es * n * mu * (1 if (world == 1 or (mu == 1 and fused) or shared_result) else world)
         d2h = es * n * mu * (1 if (world == 1 or shared_result) else world)
@@ -543,6 +551,8 @@ def run_b200(args):
             line["gmres"] = gm
         if tr_obj is not None:
             line["transposed"] = tr_obj
+        if also is not None:
+            line["also"] = also
         print(json.dumps(line), flush=True)
     barrier()
     op.close()
@@ -755,6 +765,90 @@ def run_gmres_regularised(args, world, rank, dev, threads, log, barrier):
         # (spectrum within [1e5, 1e5 + N/(4 pi)])
         out["solution_rel_diff_bound"] = "2 * tol * cond(A) <= 6e-6"
     return out
+
+
+def run_also_rhs(args, mu, op, engine, H, flat, x_vec, world, rank, dev, thr, dmma_tf, w_all, log, barrier, max_over_ranks):
+    """Y = A X for blocks of `mu` right-hand sides on the operator the single-RHS run has assembled (BASELINE.json configs[3] when mu = 64
+    on configs[1]'s operator): device-resident row-major product timed with CUDA events (max over ranks), the same through the public
+    `matmat` with page-locked host blocks, and on EVERY rank its slab of both results against the reference's
+    openmp_internal_add_hmatrix_matrix_product_row_major of its own slab.  Fewer steps than the headline (the block product is 4-10x longer)."""
+    import torch
+    import torch.distributed as dist
+
+    n, es = args.n, flat.elem_bytes
+    tdt = torch.complex128 if flat.dtype == "z" else torch.float64
+    steps, warm = max(3, min(10, args.steps)), 3
+    X_user = np.asfortranarray(np.stack([np.roll(x_vec, 7 * j) * (1.0 + 0.01 * j) for j in range(mu)], axis=1))  # as `--rhs mu` builds it
+    Xc_host = np.ascontiguousarray(X_user[flat.source_permutation])
+    Xc = torch.from_numpy(Xc_host).to(dev)
+    Yc = torch.zeros((n, mu), dtype=tdt, device=dev)
+    last = {}
+    if world > 1:
+        def step():
+            last["y"] = op.matmat_cluster_(Xc.view(-1), Yc, mu)
+    else:
+        def step():
+            engine.add_matrix_product_row_major("N", 1.0, Xc, 0.0, Yc, mu)
+            last["y"] = Yc
+    for _ in range(warm):
+        step()
+    barrier()
+    l0 = engine.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        step()
+    ev1.record()
+    barrier()
+    ms = max_over_ranks(ev0.elapsed_time(ev1)) / steps
+    launches = engine.launch_count - l0
+    y_dev = last["y"].detach().reshape(n, mu).cpu().numpy().copy()
+    # end to end: page-locked Fortran-ordered host blocks through the public matmat (N > 1: every rank moves 1/P of the rows)
+    x_blk = torch.empty(n * mu, dtype=tdt).pin_memory().numpy().reshape((n, mu), order="F")
+    x_blk[...] = X_user
+    if world > 1:
+        apply_user = lambda: op.matmat(x_blk, out="shared")  # noqa: E731
+    else:
+        y_blk = torch.empty(n * mu, dtype=tdt).pin_memory().numpy().reshape((n, mu), order="F")
+        apply_user = lambda: op.matmat(x_blk, out=y_blk)  # noqa: E731
+    for _ in range(2):
+        apply_user()
+    barrier()
+    e_steps = max(3, steps // 2)
+    t0 = time.perf_counter()
+    for _ in range(e_steps):
+        Y_user = apply_user()
+    torch.cuda.synchronize()
+    e2e_step = max_over_ranks(time.perf_counter() - t0) / e_steps
+    Y_user = np.array(Y_user, copy=True)
+    shared = world > 1 and getattr(op, "_shmb", None) is not None
+    # parity on this rank's slab, CPU baseline = the reference's row-major block product of the slab
+    o, sz = (op.offs[rank], op.sizes[rank]) if world > 1 else (0, n)
+    t_slab, ref = cpu_reference_slab(H, flat, Xc_host, mu, thr, budget_s=4.0, log=log, sync=barrier)
+    nrm = float(np.linalg.norm(ref))
+    parity = max_over_ranks(np.linalg.norm(y_dev[o:o + sz] - ref.reshape(sz, mu)) / nrm)
+    parity_e2e = max_over_ranks(np.linalg.norm(Y_user[flat.target_permutation[o:o + sz]] - ref.reshape(sz, mu)) / nrm)
+    t_max = max_over_ranks(t_slab)
+    identical = None
+    if world > 1:
+        hs = [None] * world
+        dist.all_gather_object(hs, (hashlib.blake2b(y_dev.tobytes(), digest_size=8).hexdigest(), hashlib.blake2b(Y_user.tobytes(), digest_size=8).hexdigest()))
+        identical = len(set(hs)) == 1
+    flops = (2 if flat.dtype == "d" else 8) * mu * w_all
+    tf = flops / (ms * 1e-3) / 1e12
+    log(f"also {mu} RHS: {ms:.3f} ms per block ({mu * 1e3 / ms:.0f} RHS/s), e2e {e2e_step * 1e3:.2f} ms, parity {parity:.2e} / e2e {parity_e2e:.2e}")
+    return {"metric": metric_name(args, mu), "config": config_of(args, mu), "value": round(mu * 1e3 / ms, 3), "unit": UNIT, "steps": steps, "warmup": warm,
+            "ms_per_step": round(ms, 4), "gpu_launches": int(launches),
+            "e2e": {"value": round(mu / e2e_step, 3), "unit": UNIT, "steps": e_steps, "ms_per_step": round(e2e_step * 1e3, 4),
+                    "h2d_bytes_per_step": es * n * mu * (1 if (world == 1 or shared) else world), "d2h_bytes_per_step": es * n * mu * (1 if (world == 1 or shared) else world),
+                    "api": "matmat(X, out) on page-locked Fortran-ordered host blocks, user numbering" + (" (node-shared result block, 1/P of the rows per rank over PCIe)" if shared else "")},
+            "roofline": {"bound": "tensor", "kernel": "hmatrix_mm_kernel<T,phase 1|2> panel GEMMs (mma.sync.m8n8k4.f64, SASS DMMA)", "achieved": round(tf, 2),
+                         "peak": dmma_tf * world if dmma_tf else None, "peak_source": "hmb200_fp64_rate (DMMA issue rate measured in this run) x GPUs", "unit": "TFLOP/s",
+                         "frac": round(tf / (dmma_tf * world), 4) if dmma_tf else None, "algorithmic_flops_per_step": flops},
+            "cpu_baseline": {"value": round(mu / t_max, 4), "unit": UNIT, "cores": thr * world, "kind": "reference", "ms_per_product": round(t_max * 1e3, 2),
+                             "sample": f"full {mu}-RHS row-major block products of the same operator (best of >= 2 within 4 s), reference OpenMP path" +
+                                       ("" if world == 1 else f"; emulated ranks: each of the {world} processes multiplies its own slab, value = mu / max_p t(slab_p)")},
+            "parity_rel_err_vs_reference": parity, "parity_rel_err_vs_reference_e2e": parity_e2e, "replicas_bit_identical": identical}
 
 
 def cpu_reference_slab(H, flat, x_cluster_host, mu, threads, budget_s, log, sync=None):
