@@ -67,3 +67,21 @@ def hpddm_solve(matvec, b, x0=None, args="", mu=1):
     fn.restype = ctypes.c_int
     it = fn(ctypes.c_int(n), CB(cb), None, ctypes.c_void_p(bf.ctypes.data), ctypes.c_void_p(x.ctypes.data), ctypes.c_int(mu), args.encode())
     return x, int(it), calls[0]
+
+
+def plugin_host():
+    """oracle/_ref/htool_plugin_host: the reference's own Python plugin classes (LocalRenumbering, RestrictedGlobalToLocalOperator,
+    VirtualLocalToLocalOperator; src/htool/local_operator/*.hpp) in a module without MPI + drivers through the C++ interface"""
+    if not glob.glob(os.path.join(REF_DIR, "htool_plugin_host*.so")):
+        raise RuntimeError("oracle/_ref/htool_plugin_host*.so is missing (make -C oracle ref, needs /root/reference)")
+    root = os.path.dirname(_HERE)
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    from htool_python_b200 import _blas
+
+    _blas.preload()
+    if REF_DIR not in sys.path:
+        sys.path.insert(0, REF_DIR)
+    import htool_plugin_host
+
+    return htool_plugin_host
